@@ -1,0 +1,266 @@
+/* umrs.h -- C-ABI of the B200-native batched scan core ("umrs" = ut multi-robot
+ * sim).  This is the drop-in boundary for ONE hot path of ut_multirobot_sim:
+ * the simulated 2-D laser scan plus the pose integration that feeds it.
+ *
+ * Citations are file:line in the reference tree (ut-amrl/ut_multirobot_sim).
+ * Each entry point names the reference interface it replaces:
+ *
+ *   umrs_map_create / umrs_map_load_file   VectorMap::lines after VectorMap::Load
+ *                                          (src/simulator/vector_map.h:75,78;
+ *                                           vector_map.cpp:397-411)
+ *   umrs_predicted_scan                    VectorMap::GetPredictedScan
+ *                                          (vector_map.h:66-72, vector_map.cpp:420-478)
+ *                                          called from Simulator::publishLaser
+ *                                          (simulator.cpp:405-411)
+ *   umrs_scan_batch                        the same routine over many fans
+ *   umrs_world_*                           Simulator::update + publishLaser
+ *                                          (simulator.cpp:474-509, 393-426) with
+ *                                          the EntityBase/RobotModel interface
+ *                                          (entity_base.h:45-53, robot_model.h:36-37)
+ *                                          batched over W independent worlds
+ *
+ * Conventions: extern "C"; plain pointers and sizes; every function returns an
+ * int status (UMRS_OK == 0); no exceptions and no exit() cross the boundary (the
+ * reference exit(1)s on a missing map, vector_map.cpp:399-402).  Handles are
+ * not thread-safe (the reference is single-threaded); one handle belongs to
+ * the CUDA device that was current when it was created.  There is no CPU
+ * fallback: without a usable sm_100 device every compute entry point returns
+ * UMRS_ERR_NO_DEVICE / UMRS_ERR_CUDA.
+ */
+#ifndef UMRS_H_
+#define UMRS_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UMRS_VERSION 100
+
+/* ---- status codes --------------------------------------------------------- */
+#define UMRS_OK 0
+#define UMRS_ERR_INVALID 1     /* bad argument (null pointer, negative size ...) */
+#define UMRS_ERR_CUDA 2        /* a CUDA call failed; see umrs_last_cuda_error() */
+#define UMRS_ERR_NOMEM 3       /* host or device allocation failed */
+#define UMRS_ERR_UNSUPPORTED 4 /* e.g. candidate set does not fit shared memory */
+#define UMRS_ERR_NO_DEVICE 5   /* no CUDA device / not sm_100 */
+#define UMRS_ERR_IO 6          /* map file could not be read */
+
+int umrs_version(void);
+const char* umrs_status_string(int status);
+/* Text of the last CUDA error seen by this thread's calls ("" if none). */
+const char* umrs_last_cuda_error(void);
+/* Number of kernels THIS LIBRARY has launched since load (all handles). */
+uint64_t umrs_kernel_launch_count(void);
+
+/* ---- parameter PODs (host shell fills them from its parsed Lua config) ----- */
+
+/* Robot model kinds; strings as in simulator.cpp:128-142 / sim_config.lua:51-55. */
+#define UMRS_ACKERMANN_DRIVE 0
+#define UMRS_OMNIDIRECTIONAL_DRIVE 1
+#define UMRS_DIFF_DRIVE 2
+/* "ACKERMANN_DRIVE" | "OMNIDIRECTIONAL_DRIVE" | "DIFF_DRIVE" -> kind, else -1. */
+int umrs_model_type_from_string(const char* robot_type);
+
+/* Laser keys: simulator.cpp:70-72,87-93 (laser_loc.x/.y, laser_angle_min/max/
+ * increment, laser_min_range, laser_max_range, laser_noise_stddev). */
+typedef struct umrs_laser_params {
+  float loc_x, loc_y;
+  float angle_min, angle_max, angle_increment;
+  float range_min, range_max;
+  float noise_stddev;
+} umrs_laser_params;
+
+/* num_rays exactly as simulator.cpp:402-404:
+ * int(1.0 + (angle_max - angle_min) / angle_increment), float subtraction and
+ * division, double add. */
+int umrs_laser_num_rays(const umrs_laser_params* laser);
+
+/* One robot's parameters.  Keys cited per group; unused groups are ignored. */
+typedef struct umrs_robot_params {
+  int32_t model_type; /* UMRS_ACKERMANN_DRIVE ... */
+  /* ackermann_model.cpp:16-23 (ak_*), defaults ut_automata_config.lua:4-10 */
+  float ak_min_turn_radius, ak_max_speed, ak_max_accel;
+  float ak_angular_error_bias, ak_angular_error_rate;
+  /* diff_drive_model.cpp:42-51, defaults ut_jackal_config.lua:14-21 */
+  int32_t invert_linear_vel_cmds, invert_angular_vel_cmds;
+  float linear_pos_accel_limit, linear_neg_accel_limit;
+  float angular_pos_accel_limit, angular_neg_accel_limit;
+  float max_angular, max_linear_vel;
+  /* omnidirectional_model.cpp:21-24, defaults cobot_config.lua:13-18 */
+  float co_max_accel, co_max_angle_accel, co_max_speed, co_max_angle_vel;
+  /* body (simulator.cpp:65-68; the reference only draws it, simulator.cpp:318-327,
+   * 380-383).  footprint_enabled != 0 makes the body a 4-segment rectangle that
+   * OTHER robots' scans see (new behaviour). */
+  float car_length, car_width, rear_axle_offset;
+  int32_t footprint_enabled;
+  umrs_laser_params laser;
+} umrs_robot_params;
+
+/* human_object.cpp:30-43 (hu_*), defaults human_config.lua.  mode: 0 Singleshot,
+ * 1 Repeat (human_object.h:33-36). */
+typedef struct umrs_human_params {
+  float radius;
+  int32_t num_segments;
+  float start_x, start_y, start_theta;
+  float goal_x, goal_y, goal_theta;
+  float max_speed, avg_speed, max_omega, avg_omega;
+  float reach_goal_threshold;
+  int32_t mode;
+} umrs_human_params;
+
+/* Defaults restating the reference's config files (values cited above). */
+void umrs_default_laser(umrs_laser_params* out);            /* sim_config.lua:31,39-44 */
+void umrs_default_jackal_laser(umrs_laser_params* out);     /* ut_jackal_config.lua:39,44-48 */
+void umrs_default_ut_automata(umrs_robot_params* out);      /* ut_automata_config.lua + sim_config.lua:25-31 */
+void umrs_default_ut_jackal(umrs_robot_params* out);        /* ut_jackal_config.lua */
+void umrs_default_bwibot(umrs_robot_params* out);           /* bwibot_config.lua */
+void umrs_default_cobot(umrs_robot_params* out);            /* cobot_config.lua */
+void umrs_default_human(umrs_human_params* out);            /* human_config.lua */
+
+/* LaserScan-shaped header, fields as Simulator::init sets them
+ * (simulator.cpp:150-159): time_increment 0, scan_time 0.05, intensities empty. */
+typedef struct umrs_laser_scan_header {
+  float angle_min, angle_max, angle_increment;
+  float time_increment, scan_time;
+  float range_min, range_max;
+  int32_t num_rays;       /* length of ranges[] */
+  int32_t ranges_offset;  /* offset of this robot's ranges inside one world's block */
+} umrs_laser_scan_header;
+
+/* ---- map -------------------------------------------------------------------- */
+typedef struct umrs_map umrs_map;
+
+/* segs_xyxy: n segments {x0,y0,x1,y1}, ALREADY cleaned by the host shell
+ * (VectorMap::Cleanup, vector_map.cpp:367-395).  Copied to the device. */
+int umrs_map_create(const float* segs_xyxy, int32_t n, umrs_map** out);
+/* Reads the reference's text format "%f,%f,%f,%f" per line (vector_map.cpp:404-407)
+ * and runs the host-side restatement of Cleanup (umrs_map_cleanup). */
+int umrs_map_load_file(const char* path, umrs_map** out);
+int umrs_map_destroy(umrs_map* map);
+int umrs_map_num_segments(const umrs_map* map, int32_t* n);
+/* Copies the (cleaned) host segments out; cap in segments. */
+int umrs_map_get_segments(const umrs_map* map, float* segs_xyxy, int32_t cap);
+
+/* Host-only helper, no device needed: VectorMap::Cleanup + ShrinkLine
+ * (vector_map.cpp:359-395) on raw segments.  out must hold cap segments;
+ * *n_out receives the cleaned count (UMRS_ERR_INVALID if cap is too small). */
+int umrs_map_cleanup(const float* segs_xyxy, int32_t n, float* out_xyxy,
+                     int32_t cap, int32_t* n_out);
+
+/* ---- drop-in scan -------------------------------------------------------------
+ * Same seven arguments as VectorMap::GetPredictedScan (vector_map.h:66-72) plus
+ * the object lines the reference keeps in VectorMap::object_lines
+ * (vector_map.h:81).  Host buffers, synchronous.  ranges_out: num_rays floats.
+ * hit_idx_out (nullable): index of the hit segment in map-then-object order
+ * (GetSceneLines order, vector_map.cpp:200-214), -1 where nothing covers the
+ * ray (range == range_max).  range_min is ignored, as in the reference. */
+int umrs_predicted_scan(umrs_map* map, const float* obj_segs_xyxy, int32_t n_obj,
+                        float loc_x, float loc_y, float range_min, float range_max,
+                        float angle_min, float angle_max, int32_t num_rays,
+                        float* ranges_out, int32_t* hit_idx_out);
+
+/* Many fans against one map (+ one shared object-line set).  fans: n_fans x
+ * {loc_x, loc_y, angle_min, angle_max}.  Output [n_fans][num_rays].  Host
+ * buffers, synchronous.  Uses the shared-memory kernel when the candidate set
+ * fits, else the uniform-grid walk. */
+int umrs_scan_batch(umrs_map* map, const float* obj_segs_xyxy, int32_t n_obj,
+                    const float* fans, int32_t n_fans, float range_max,
+                    int32_t num_rays, float* ranges_out, int32_t* hit_idx_out);
+/* Same with device-resident fans/outputs on a caller stream (cudaStream_t as
+ * void*, NULL = default stream); asynchronous. */
+int umrs_scan_batch_device(umrs_map* map, const float* obj_segs_dev, int32_t n_obj,
+                           const float* fans_dev, int32_t n_fans, float range_max,
+                           int32_t num_rays, float* ranges_dev, int32_t* hit_idx_dev,
+                           void* stream);
+/* Which kernel umrs_scan_batch* would pick for this map: 0 = shared-memory
+ * (K1), 1 = uniform grid (K2).  force: -1 auto, 0, 1. */
+int umrs_map_set_scan_kernel(umrs_map* map, int32_t force);
+
+/* ---- batched worlds ------------------------------------------------------------
+ * W independent worlds stepping in lockstep; every world has the same robot
+ * roster (robots[r] describes robot r of every world), H humans and O static
+ * square objects (ShortTermObject, short_term_object.cpp:53-58), all against
+ * one shared static map. */
+typedef struct umrs_world umrs_world;
+
+typedef struct umrs_world_desc {
+  int32_t num_worlds;
+  int32_t robots_per_world;
+  int32_t humans_per_world;
+  int32_t static_objects_per_world;
+  const umrs_robot_params* robots; /* [robots_per_world] */
+  const umrs_human_params* humans; /* [humans_per_world], per-world start/goal via set_humans */
+  float dt;                        /* delta_t, sim_config.lua:17 */
+  uint64_t seed;                   /* Philox key */
+  int32_t laser_noise_enabled;     /* 0: ranges are GetPredictedScan's, untouched */
+  int32_t motion_noise_enabled;    /* 0: Ackermann angular error draws are 0 */
+  int32_t world_index_base;        /* global index of world 0 (multi-GPU shards) */
+  int32_t write_hit_idx;           /* keep the hit-segment index buffer */
+} umrs_world_desc;
+
+int umrs_world_create(umrs_map* map, const umrs_world_desc* desc, umrs_world** out);
+int umrs_world_destroy(umrs_world* world);
+
+/* Rays of one world = sum over robots of num_rays; ranges buffer is
+ * [num_worlds][rays_per_world]. */
+int umrs_world_rays_per_world(const umrs_world* world, int32_t* n);
+int umrs_world_scan_header(const umrs_world* world, int32_t robot,
+                           umrs_laser_scan_header* out);
+/* Object lines of one world: [static objects][humans][robot footprints]. */
+int umrs_world_object_lines_per_world(const umrs_world* world, int32_t* n);
+
+/* EntityBase::SetPose / RobotModel::SetVel for every robot: [W][R][3] {x,y,theta}.
+ * vel may be NULL (zeros).  Resets command state.  Host buffers. */
+int umrs_world_set_robot_state(umrs_world* world, const float* pose_xyt,
+                               const float* vel_xyt);
+int umrs_world_get_robot_state(umrs_world* world, float* pose_xyt, float* vel_xyt);
+/* start/goal: [W][H][3]; pose := start (HumanObject ctor, human_object.cpp:83-85).
+ * NULL keeps the desc's values for every world. */
+int umrs_world_set_humans(umrs_world* world, const float* start_xyt,
+                          const float* goal_xyt);
+int umrs_world_get_human_poses(umrs_world* world, float* pose_xyt);
+/* [W][O][3] */
+int umrs_world_set_static_objects(umrs_world* world, const float* pose_xyt);
+/* Current object lines [W][L][4] (after the last step). */
+int umrs_world_get_object_lines(umrs_world* world, float* segs_xyxy);
+
+/* One tick = Simulator::update + publishLaser for every world.
+ * cmds: [W][R][3] floats; Ackermann {velocity, curvature, -}
+ * (AckermannCurvatureDriveMsg.msg:5,11), diff-drive {linear.x, angular.z, -},
+ * omni {velocity_x, velocity_y, velocity_r}.  cmd_mask (nullable): [W][R] bytes,
+ * 0 = no new command this tick (the watchdog then ages the old one in SIM time:
+ * a command older than 0.1 s is zeroed, ackermann_model.cpp:55-58).
+ * Host version copies cmds in and ranges (and idx, if non-NULL) out, synchronous. */
+int umrs_world_step(umrs_world* world, const float* cmds, const uint8_t* cmd_mask,
+                    float* ranges_out, int32_t* hit_idx_out);
+/* Device version: cmds/mask already on the device, results stay there.  Async on
+ * stream (cudaStream_t as void*; NULL = the handle's own stream). */
+int umrs_world_step_device(umrs_world* world, const float* cmds_dev,
+                           const uint8_t* cmd_mask_dev, void* stream);
+/* Device-resident outputs of the last step (owned by the handle). */
+int umrs_world_device_buffers(umrs_world* world, float** ranges_dev,
+                              int32_t** hit_idx_dev, float** robot_pose_dev);
+int umrs_world_sync(umrs_world* world);
+int umrs_world_step_count(const umrs_world* world, uint64_t* steps);
+
+/* Work accounting for the roofline: candidate ray-segment tests executed and
+ * candidate segments pre-processed by the scan kernel in the last step (counted
+ * on the device when enabled; costs a few atomics per CTA). */
+int umrs_world_enable_counters(umrs_world* world, int32_t on);
+int umrs_world_read_counters(umrs_world* world, uint64_t* ray_seg_tests,
+                             uint64_t* segs_prepared, uint64_t* chunk_seg_pairs);
+
+/* K3: per-shard statistics of the last step's ranges (count of hits, min, max,
+ * sum), reduced on the device; 4 doubles out.  Host buffer. */
+int umrs_world_stats(umrs_world* world, double* out4);
+
+/* Philox4x32-10 as used for the noise (host restatement for tests):
+ * counter {c0,c1,c2,c3}, key {k0,k1} -> 4 words. */
+void umrs_philox4x32(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UMRS_H_ */

@@ -1,0 +1,129 @@
+// Device-side primitives of the scan core (sm_100a).  Citations are file:line
+// in the reference tree (ut-amrl/ut_multirobot_sim).
+//
+// Exactness discipline: this translation unit is compiled with -fmad=false and
+// WITHOUT --use_fast_math, so every float * + - / sqrtf below is one IEEE
+// round-to-nearest operation, exactly like the reference built with
+// -ffp-contract=off.  The places where the reference's expression promotes to
+// double (atan2, cos/sin in vector_map.cpp, AngleMod's rint) use double here too.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/umrs.h"
+
+namespace umrs {
+
+constexpr double kPiD = 3.14159265358979323846;
+constexpr double k2PiD = 2.0 * kPiD;                 // M_2PI, math_util.h:28-30
+constexpr float k2PiF = 6.28318530717958647692f;     // T(M_2PI) for T = float
+
+// math_util::AngleMod<float>, math_util.h:55-59 (rint is the double C function
+// in vector_map.cpp's translation unit; the product and subtraction promote).
+__device__ __forceinline__ float angle_mod_f(float angle) {
+  const float q = angle / k2PiF;
+  const double k = rint((double)q);
+  return (float)((double)angle - (double)k2PiF * k);
+}
+// math_util::AngleMod<double>
+__device__ __forceinline__ double angle_mod_d(double angle) {
+  return angle - k2PiD * rint(angle / k2PiD);
+}
+
+// Ray angle i of a fan: vector_map.cpp:465,467.
+__device__ __forceinline__ float ray_angle(float angle_min, float da, int i) {
+  return angle_mod_f(angle_min + (float)i * da);
+}
+
+// Per-candidate constants of the ray fill (vector_map.cpp:444-459,471,473).
+// wraps_around is not stored: after the reference's swap, a wrapping interval
+// has a0 > a1 and a plain one a0 < a1 (|a0-a1| >= 1e-4 is guaranteed), so
+// wraps == (a0 > a1).
+struct SegCast {
+  float a0, a1, nx, ny;  // one LDS.128 in the ray loop
+  float c;               // n . p0'
+  bool valid;
+  float arc;             // CCW extent a0 -> a1 in [0, pi], for chunk culling only
+};
+
+__device__ __forceinline__ SegCast make_cast(float4 s, float lx, float ly) {
+  SegCast k;
+  k.valid = false;
+  k.a0 = 0.f; k.a1 = 0.f; k.nx = 0.f; k.ny = 0.f; k.c = 0.f; k.arc = 0.f;
+  float p0x = s.x - lx, p0y = s.y - ly;   // :447-448
+  float p1x = s.z - lx, p1y = s.w - ly;
+  float a0 = (float)atan2((double)p0y, (double)p0x);  // :449-450 (double atan2)
+  float a1 = (float)atan2((double)p1y, (double)p1x);
+  if (fabs((double)(a0 - a1)) < 0.0001) return k;     // :451
+  const bool wraps = fabs((double)(a1 - a0)) > kPiD;  // :452
+  if ((wraps && a0 < a1) || (!wraps && a0 > a1)) {    // :453-457
+    float t;
+    t = a0; a0 = a1; a1 = t;
+    t = p0x; p0x = p1x; p1x = t;
+    t = p0y; p0y = p1y; p1y = t;
+  }
+  // UnitNormal = Perp(Dir()), line2d.h:62-69; Eigen normalized() divides.
+  float dx = p1x - p0x, dy = p1y - p0y;
+  const float z = dx * dx + dy * dy;
+  if (z > 0.0f) {
+    const float len = sqrtf(z);
+    dx = dx / len;
+    dy = dy / len;
+  }
+  k.a0 = a0;
+  k.a1 = a1;
+  k.nx = -dy;
+  k.ny = dx;
+  k.c = k.nx * p0x + k.ny * p0y;   // :473 n.dot(p0)
+  k.valid = true;
+  k.arc = wraps ? (a1 + k2PiF) - a0 : a1 - a0;
+  return k;
+}
+
+// vector_map.cpp:469-470, inclusive at both ends.
+__device__ __forceinline__ bool cast_covers(float a0, float a1, float a) {
+  const bool p = a0 <= a, q = a1 >= a;
+  return (a0 > a1) ? (p || q) : (p && q);
+}
+
+// GetSceneLines AABB cull, vector_map.cpp:195-204.
+__device__ __forceinline__ bool aabb_keep(float4 s, float lx, float ly, float max_range) {
+  const float x_min = lx - max_range, y_min = ly - max_range;
+  const float x_max = lx + max_range, y_max = ly + max_range;
+  if (s.x < x_min && s.z < x_min) return false;
+  if (s.y < y_min && s.w < y_min) return false;
+  if (s.x > x_max && s.z > x_max) return false;
+  if (s.y > y_max && s.w > y_max) return false;
+  return true;
+}
+
+// ---- Philox4x32-10 (counter-based; replaces std::default_random_engine,
+// simulator.h:99-100, ackermann_model.h:17-18) ------------------------------
+__device__ __forceinline__ uint4 philox4x32(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+
+// Box-Muller on two words -> two N(0,1).
+__device__ __forceinline__ float2 box_muller(uint32_t u0, uint32_t u1) {
+  const float x = ((float)(u0 >> 8) + 0.5f) * (1.0f / 16777216.0f);
+  const float y = ((float)(u1 >> 8) + 0.5f) * (1.0f / 16777216.0f);
+  const float r = sqrtf(-2.0f * logf(x));
+  float s, c;
+  sincosf(k2PiF * y, &s, &c);
+  return make_float2(r * c, r * s);
+}
+
+// Noise streams (counter.w): which consumer draws.
+constexpr uint32_t kStreamLaser = 0x4C415352u;   // per-ray range noise
+constexpr uint32_t kStreamMotion = 0x4D4F5445u;  // Ackermann angular error
+
+}  // namespace umrs

@@ -1,0 +1,103 @@
+// Internal host<->kernel contract of libumrs (not part of the C-ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/umrs.h"
+
+namespace umrs {
+
+// ---- device-resident world state (one record per entity, 64 B) ---------------
+// Mirrors the members the reference keeps per model instance:
+// EntityBase::pose_ (entity_base.h:36), RobotModel::vel_ (robot_model.h:31),
+// last_cmd_/target_*_vel_ + t_last_cmd_ (ackermann_model.h:15-16,
+// diff_drive_model.h:28-29), DiffDriveModel::linear_vel_/angular_vel_ (double,
+// diff_drive_model.h:30-31).
+struct RobotState {
+  float pose[3];
+  float vel[3];
+  float cmd[3];
+  int32_t cmd_age;  // ticks since the last accepted command (sim-time watchdog)
+  double linear_vel;
+  double angular_vel;
+  float pad[2];
+};
+static_assert(sizeof(RobotState) == 64, "RobotState must be 64 B");
+
+// HumanObject members, human_object.h:40-52.
+struct HumanState {
+  float pose[3];
+  float start[3];
+  float goal[3];
+  float trans_vel[2];
+  float rot_vel;
+  float pad[4];
+};
+static_assert(sizeof(HumanState) == 64, "HumanState must be 64 B");
+
+constexpr int kAgeNever = 1 << 28;
+constexpr int kScanThreads = 128;  // 4 warps per fan CTA
+
+// ---- K1 parameters -------------------------------------------------------------
+struct ScanCommon {
+  const float4* map_segs;  // cleaned map, {x0,y0,x1,y1} per segment
+  int32_t n_map;
+  float* ranges;           // [fans][num_rays] or [W][rays_per_world]
+  int32_t* hit_idx;        // nullable, same shape
+  unsigned long long* counters;  // nullable: {tests, segs_prepared, chunk_seg_pairs}
+};
+
+struct ScanBatchParams {
+  ScanCommon c;
+  const float4* obj_segs;  // shared object lines (nullable)
+  int32_t n_obj;
+  const float4* fans;      // {loc_x, loc_y, angle_min, angle_max}
+  int32_t n_fans;
+  float range_max;
+  int32_t num_rays;
+};
+
+struct WorldStepParams {
+  ScanCommon c;
+  int32_t W, R, H, O;
+  const umrs_robot_params* robots;  // [R]
+  const umrs_human_params* humans;  // [H]
+  const float4* tmpl;               // [L_obj] template line of world-line l
+  const int16_t* line_ent;          // [L_obj] entity of world-line l
+  const int32_t* ent_off;           // [O+H+R+1] first world-line of entity e
+  int32_t L_obj;
+  const RobotState* rs_in;
+  RobotState* rs_out;
+  const HumanState* hs_in;
+  HumanState* hs_out;
+  const float* static_pose;  // [W][O][3]
+  const float* cmds;         // [W][R][3]
+  const uint8_t* cmd_mask;   // nullable [W][R]
+  const int32_t* ray_off;    // [R+1]
+  const int32_t* num_rays;   // [R]
+  int32_t rays_per_world;
+  float4* fan_params;        // [W][R] {loc_x, loc_y, angle_min, angle_max} used
+  float4* obj_lines_out;     // [W][L_obj]
+  float* robot_pose_out;     // [W][R][3] (convenience copy for consumers)
+  float dt;
+  uint32_t key0, key1;
+  uint32_t step_lo, step_hi;
+  int32_t world_base;
+  int32_t laser_noise, motion_noise;
+};
+
+// Dynamic shared memory a K1 CTA needs for n_cand candidates (+ n_obj world
+// lines and n_ent entities when the step is fused).
+size_t k1_smem_bytes(int n_cand, int n_obj_lines, int n_ent);
+
+cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream);
+cudaError_t launch_world_step(const WorldStepParams& p, cudaStream_t stream);
+cudaError_t launch_stats(const float* ranges, size_t n, double* out4_dev,
+                         cudaStream_t stream);
+cudaError_t k1_configure(size_t smem_bytes);
+
+// Launch accounting (umrs_kernel_launch_count).
+void note_launch(int n = 1);
+
+}  // namespace umrs
