@@ -242,6 +242,10 @@ int umrs_world_step_device(umrs_world* world, const float* cmds_dev,
 /* Device-resident outputs of the last step (owned by the handle). */
 int umrs_world_device_buffers(umrs_world* world, float** ranges_dev,
                               int32_t** hit_idx_dev, float** robot_pose_dev);
+/* Fan parameters the last step used: [W][R][4] {loc_x, loc_y, angle_min, angle_max}
+ * in the world frame (laser origin simulator.cpp:398-400, angle_min + theta
+ * :408-409), so a checker can hand the oracle the identical fan.  Host buffer. */
+int umrs_world_get_fan_params(umrs_world* world, float* out);
 int umrs_world_sync(umrs_world* world);
 int umrs_world_step_count(const umrs_world* world, uint64_t* steps);
 

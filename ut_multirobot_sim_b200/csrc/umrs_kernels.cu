@@ -389,3 +389,195 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
     }
   }
 }
+
+// ---- fused world-step kernel -------------------------------------------------
+// grid = W * R fans; CTA (w, r).  Every CTA of world w integrates ALL entities of
+// that world (R + H tiny steps, redundantly across the R CTAs) from the
+// read-only "in" state so that no inter-CTA exchange is needed; the r == 0 CTA
+// alone writes the "out" state (ping-pong buffers).  Order as in
+// Simulator::Run (simulator.cpp:531-541): update() first, scan from the
+// post-step pose against the post-step object lines.
+__global__ void __launch_bounds__(kScanThreads)
+k1_world_step(const __grid_constant__ WorldStepParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int n_cand = p.c.n_map + p.L_obj;
+  const int n_ent = p.O + p.H + p.R;
+  const SmemView sm = carve(smem_raw, n_cand, p.L_obj);
+  const int w = blockIdx.x / p.R;
+  const int r = blockIdx.x - w * p.R;
+  const bool owner = (r == 0);
+  const double dt = (double)p.dt;  // `const double& dt` bound to float CONFIG_DT
+  const int t = threadIdx.x;
+
+  // ---- phase A: entity steps -> sm.ent[e] = {x, y, theta, sin, cos} ----------
+  for (int e = t; e < n_ent; e += blockDim.x) {
+    float px, py, pth;
+    if (e < p.O) {
+      const float* sp = p.static_pose + ((size_t)w * p.O + e) * 3;
+      px = sp[0]; py = sp[1]; pth = sp[2];
+    } else if (e < p.O + p.H) {
+      const int h = e - p.O;
+      HumanState s = p.hs_in[(size_t)w * p.H + h];
+      human_step(s, p.humans[h], dt);
+      if (owner) p.hs_out[(size_t)w * p.H + h] = s;
+      px = s.pose[0]; py = s.pose[1]; pth = s.pose[2];
+    } else {
+      const int rr = e - p.O - p.H;
+      const size_t gi = (size_t)w * p.R + rr;
+      RobotState s = p.rs_in[gi];
+      const umrs_robot_params& rp = p.robots[rr];
+      if (p.cmds != nullptr && (p.cmd_mask == nullptr || p.cmd_mask[gi] != 0)) {
+        const float cmd[3] = {p.cmds[gi * 3 + 0], p.cmds[gi * 3 + 1], p.cmds[gi * 3 + 2]};
+        robot_command(s, rp, cmd);
+      }
+      float n1 = 0.f, n2 = 0.f;
+      if (p.motion_noise && rp.model_type == UMRS_ACKERMANN_DRIVE) {
+        const uint4 wd = philox4x32(
+            make_uint4(0u, (uint32_t)(p.world_base + w) * (uint32_t)p.R + (uint32_t)rr,
+                       p.step_lo, p.step_hi ^ kStreamMotion),
+            make_uint2(p.key0, p.key1));
+        const float2 g = box_muller(wd.x, wd.y);
+        n1 = g.x; n2 = g.y;
+      }
+      robot_step(s, rp, dt, n1, n2);
+      if (owner) {
+        p.rs_out[gi] = s;
+        if (p.robot_pose_out != nullptr) {
+          p.robot_pose_out[gi * 3 + 0] = s.pose[0];
+          p.robot_pose_out[gi * 3 + 1] = s.pose[1];
+          p.robot_pose_out[gi * 3 + 2] = s.pose[2];
+        }
+      }
+      px = s.pose[0]; py = s.pose[1]; pth = s.pose[2];
+    }
+    // HumanObject::Transform rotation, human_object.cpp:132: R(AngleMod(angle))
+    const float am = angle_mod_f(pth);
+    float* en = sm.ent + 5 * e;
+    en[0] = px; en[1] = py; en[2] = pth;
+    en[3] = sinf(am); en[4] = cosf(am);
+  }
+  __syncthreads();
+
+  // ---- object lines: R * template + T (human_object.cpp:135-138) --------------
+  for (int l = t; l < p.L_obj; l += blockDim.x) {
+    const int e = p.line_ent[l];
+    const float4 tm = __ldg(p.tmpl + l);
+    const float* en = sm.ent + 5 * e;
+    const float sn = en[3], cs = en[4];
+    float4 o;
+    o.x = (cs * tm.x - sn * tm.y) + en[0];
+    o.y = (sn * tm.x + cs * tm.y) + en[1];
+    o.z = (cs * tm.z - sn * tm.w) + en[0];
+    o.w = (sn * tm.z + cs * tm.w) + en[1];
+    sm.obj[l] = o;
+    if (owner && p.obj_lines_out != nullptr) p.obj_lines_out[(size_t)w * p.L_obj + l] = o;
+  }
+
+  // ---- fan of robot r (simulator.cpp:398-411) ----------------------------------
+  const umrs_robot_params& me = p.robots[r];
+  const float* en = sm.ent + 5 * (p.O + p.H + r);
+  Fan fan;
+  {
+    // laserLoc = t + Rotation2Df(angle) * (laser_x, laser_y): sin/cos of the raw
+    // pose angle (float overloads inside Eigen)
+    const float sn = sinf(en[2]), cs = cosf(en[2]);
+    fan.lx = en[0] + (cs * me.laser.loc_x - sn * me.laser.loc_y);
+    fan.ly = en[1] + (sn * me.laser.loc_x + cs * me.laser.loc_y);
+    fan.amin = me.laser.angle_min + en[2];
+    fan.amax = me.laser.angle_max + en[2];
+    fan.num_rays = p.num_rays[r];
+    fan.range_max = me.laser.range_max;
+  }
+  if (t == 0 && p.fan_params != nullptr)
+    p.fan_params[blockIdx.x] = make_float4(fan.lx, fan.ly, fan.amin, fan.amax);
+  __syncthreads();
+
+  const int skip_lo = p.ent_off[p.O + p.H + r], skip_hi = p.ent_off[p.O + p.H + r + 1];
+  prepass(sm, fan, p.c.map_segs, p.c.n_map, sm.obj, p.L_obj, skip_lo, skip_hi, p.c.counters);
+  __syncthreads();
+
+  PostProcess post;
+  post.enabled = p.laser_noise != 0;
+  post.stddev = me.laser.noise_stddev;
+  post.key0 = p.key0; post.key1 = p.key1;
+  post.step_lo = p.step_lo; post.step_hi = p.step_hi;
+  post.fan_global = (uint32_t)(p.world_base + w) * (uint32_t)p.R + (uint32_t)r;
+  const size_t off = (size_t)w * (size_t)p.rays_per_world + (size_t)p.ray_off[r];
+  ray_loop(sm, fan, n_cand, p.c.ranges + off,
+           p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, p.c.counters);
+}
+
+// ---- K3: statistics of a ranges buffer -------------------------------------------
+// out4 = {count of finite positive ranges, min, max, sum}; one atomic set per CTA.
+__global__ void k3_stats(const float* __restrict__ ranges, size_t n, double* out4) {
+  double cnt = 0.0, sum = 0.0;
+  float mn = __int_as_float(0x7f800000), mx = 0.f;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const float v = ranges[i];
+    if (v > 0.f && v < __int_as_float(0x7f800000)) {
+      cnt += 1.0; sum += (double)v;
+      mn = fminf(mn, v); mx = fmaxf(mx, v);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+    sum += __shfl_down_sync(0xffffffffu, sum, o);
+    mn = fminf(mn, __shfl_down_sync(0xffffffffu, mn, o));
+    mx = fmaxf(mx, __shfl_down_sync(0xffffffffu, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(out4 + 0, cnt);
+    atomicAdd(out4 + 3, sum);
+    // positive floats order like their bit patterns
+    atomicMin(reinterpret_cast<unsigned long long*>(out4 + 1),
+              (unsigned long long)__float_as_uint(mn));
+    atomicMax(reinterpret_cast<unsigned long long*>(out4 + 2),
+              (unsigned long long)__float_as_uint(mx));
+  }
+}
+
+// ---- launchers ----------------------------------------------------------------
+static size_t g_k1_smem_configured = 0;
+
+cudaError_t k1_configure(size_t smem_bytes) {
+  if (smem_bytes <= g_k1_smem_configured) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(k1_scan_batch, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem_bytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k1_world_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)smem_bytes);
+  if (e != cudaSuccess) return e;
+  g_k1_smem_configured = smem_bytes;
+  return cudaSuccess;
+}
+
+cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream) {
+  if (p.n_fans <= 0) return cudaSuccess;
+  const size_t smem = k1_smem_bytes(p.c.n_map + p.n_obj, 0, 0);
+  cudaError_t e = k1_configure(smem);
+  if (e != cudaSuccess) return e;
+  k1_scan_batch<<<p.n_fans, kScanThreads, smem, stream>>>(p);
+  note_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_world_step(const WorldStepParams& p, cudaStream_t stream) {
+  const int fans = p.W * p.R;
+  if (fans <= 0) return cudaSuccess;
+  const size_t smem = k1_smem_bytes(p.c.n_map + p.L_obj, p.L_obj, p.O + p.H + p.R);
+  cudaError_t e = k1_configure(smem);
+  if (e != cudaSuccess) return e;
+  k1_world_step<<<fans, kScanThreads, smem, stream>>>(p);
+  note_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_stats(const float* ranges, size_t n, double* out4_dev, cudaStream_t stream) {
+  // out4_dev must be pre-initialised by the caller: {0, bits(+inf), 0, 0}
+  k3_stats<<<148 * 4, 256, 0, stream>>>(ranges, n, out4_dev);
+  note_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace umrs

@@ -1,0 +1,468 @@
+// C-ABI, batched worlds (include/umrs.h: umrs_world_*).  Replaces
+// Simulator::update + publishLaser (simulator.cpp:474-509, 393-426) for W
+// independent worlds in lockstep.  Device state is ping-ponged between two
+// buffers so that the fan CTAs of one world can all read the old state.
+#include <cuda_runtime.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "../../include/umrs.h"
+#include "umrs_host.h"
+#include "umrs_internal.h"
+
+using namespace umrs;
+
+// from umrs_capi.cu
+struct umrs_map;
+namespace umrs {
+int capi_cuda_fail(cudaError_t e, const char* what);
+void capi_set_error(const char* msg);
+struct MapView { const float4* d_segs; int32_t n; int smem_optin; };
+MapView capi_map_view(const umrs_map* m);
+}  // namespace umrs
+
+#define UMRS_CUDA(call)                                          \
+  do {                                                           \
+    cudaError_t e__ = (call);                                    \
+    if (e__ != cudaSuccess) return capi_cuda_fail(e__, #call);   \
+  } while (0)
+
+struct umrs_world {
+  umrs_world_desc desc;
+  std::vector<umrs_robot_params> robots;
+  std::vector<umrs_human_params> humans;
+  MapView map;
+  int32_t W = 0, R = 0, H = 0, O = 0;
+  int32_t L_obj = 0, rays_per_world = 0;
+  std::vector<int32_t> ent_off, ray_off, num_rays;
+  cudaStream_t stream = nullptr;
+  uint64_t step = 0;
+  int cur = 0;  // index of the "in" state buffer
+  // device
+  umrs_robot_params* d_robots = nullptr;
+  umrs_human_params* d_humans = nullptr;
+  float4* d_tmpl = nullptr;
+  int16_t* d_line_ent = nullptr;
+  int32_t* d_ent_off = nullptr;
+  int32_t* d_ray_off = nullptr;
+  int32_t* d_num_rays = nullptr;
+  RobotState* d_rs[2] = {nullptr, nullptr};
+  HumanState* d_hs[2] = {nullptr, nullptr};
+  float* d_static = nullptr;
+  float* d_cmds = nullptr;
+  uint8_t* d_mask = nullptr;
+  float* d_ranges = nullptr;
+  int32_t* d_idx = nullptr;
+  float4* d_fan_params = nullptr;
+  float4* d_obj_lines = nullptr;
+  float* d_pose = nullptr;
+  unsigned long long* d_counters = nullptr;
+  bool counters_on = false;
+  double* d_stats = nullptr;
+};
+
+template <typename T>
+static cudaError_t dalloc(T** p, size_t n) {
+  return cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * (n > 0 ? n : 1));
+}
+
+extern "C" {
+
+int umrs_world_destroy(umrs_world* w) {
+  if (w == NULL) return UMRS_OK;
+  void* ptrs[] = {w->d_robots, w->d_humans, w->d_tmpl, w->d_line_ent, w->d_ent_off,
+                  w->d_ray_off, w->d_num_rays, w->d_rs[0], w->d_rs[1], w->d_hs[0],
+                  w->d_hs[1], w->d_static, w->d_cmds, w->d_mask, w->d_ranges, w->d_idx,
+                  w->d_fan_params, w->d_obj_lines, w->d_pose, w->d_counters, w->d_stats};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  if (w->stream) cudaStreamDestroy(w->stream);
+  delete w;
+  return UMRS_OK;
+}
+
+int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out) {
+  if (out == NULL) return UMRS_ERR_INVALID;
+  *out = NULL;
+  if (map == NULL || d == NULL || d->num_worlds <= 0 || d->robots_per_world <= 0 ||
+      d->humans_per_world < 0 || d->static_objects_per_world < 0 || d->robots == NULL ||
+      (d->humans_per_world > 0 && d->humans == NULL) || !(d->dt > 0.f))
+    return UMRS_ERR_INVALID;
+  umrs_world* w = new (std::nothrow) umrs_world();
+  if (!w) return UMRS_ERR_NOMEM;
+  w->desc = *d;
+  w->W = d->num_worlds; w->R = d->robots_per_world;
+  w->H = d->humans_per_world; w->O = d->static_objects_per_world;
+  w->robots.assign(d->robots, d->robots + w->R);
+  if (w->H > 0) w->humans.assign(d->humans, d->humans + w->H);
+  w->desc.robots = nullptr;
+  w->desc.humans = nullptr;
+  w->map = capi_map_view(map);
+
+  // ---- object-line roster: [statics][humans][robot bodies] ---------------------
+  std::vector<float> tmpl;      // xyxy per world-line
+  std::vector<int16_t> line_ent;
+  w->ent_off.assign(1, 0);
+  auto add_entity = [&](const float* t, int n_lines) {
+    const int e = (int)w->ent_off.size() - 1;
+    for (int i = 0; i < n_lines; ++i) {
+      tmpl.insert(tmpl.end(), t + 4 * i, t + 4 * i + 4);
+      line_ent.push_back((int16_t)e);
+    }
+    w->ent_off.push_back(w->ent_off.back() + n_lines);
+  };
+  float sq[16];
+  SquareTemplate(sq);
+  for (int o = 0; o < w->O; ++o) add_entity(sq, 4);
+  for (int h = 0; h < w->H; ++h) {
+    if (w->humans[h].num_segments < 0 || w->humans[h].num_segments > 4096) {
+      umrs_world_destroy(w);
+      return UMRS_ERR_INVALID;
+    }
+    std::vector<float> ht;
+    HumanTemplate(w->humans[h], &ht);
+    add_entity(ht.data(), (int)(ht.size() / 4));
+  }
+  for (int r = 0; r < w->R; ++r) {
+    float rt[16];
+    RobotTemplate(w->robots[r], rt);
+    add_entity(rt, w->robots[r].footprint_enabled ? 4 : 0);
+  }
+  w->L_obj = w->ent_off.back();
+  if (w->O + w->H + w->R > 32767) {
+    umrs_world_destroy(w);
+    return UMRS_ERR_UNSUPPORTED;
+  }
+
+  // ---- rays -----------------------------------------------------------------------
+  w->ray_off.assign(1, 0);
+  for (int r = 0; r < w->R; ++r) {
+    const int n = umrs_laser_num_rays(&w->robots[r].laser);
+    if (n <= 0 || !(w->robots[r].laser.angle_max > w->robots[r].laser.angle_min)) {
+      umrs_world_destroy(w);
+      return UMRS_ERR_INVALID;
+    }
+    w->num_rays.push_back(n);
+    w->ray_off.push_back(w->ray_off.back() + n);
+  }
+  w->rays_per_world = w->ray_off.back();
+
+  const size_t smem = k1_smem_bytes(w->map.n + w->L_obj, w->L_obj, w->O + w->H + w->R);
+  if (smem > (size_t)w->map.smem_optin) {
+    capi_set_error("world candidate set does not fit shared memory");
+    umrs_world_destroy(w);
+    return UMRS_ERR_UNSUPPORTED;
+  }
+
+  // ---- device allocations -----------------------------------------------------------
+  const size_t WR = (size_t)w->W * w->R, WH = (size_t)w->W * w->H, WO = (size_t)w->W * w->O;
+  const size_t n_rays = (size_t)w->W * w->rays_per_world;
+  cudaError_t e = cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking);
+  auto ok = [&]() { return e == cudaSuccess; };
+  if (ok()) e = dalloc(&w->d_robots, (size_t)w->R);
+  if (ok()) e = dalloc(&w->d_humans, (size_t)w->H);
+  if (ok()) e = dalloc(&w->d_tmpl, (size_t)w->L_obj);
+  if (ok()) e = dalloc(&w->d_line_ent, (size_t)w->L_obj);
+  if (ok()) e = dalloc(&w->d_ent_off, w->ent_off.size());
+  if (ok()) e = dalloc(&w->d_ray_off, w->ray_off.size());
+  if (ok()) e = dalloc(&w->d_num_rays, (size_t)w->R);
+  for (int b = 0; b < 2; ++b) {
+    if (ok()) e = dalloc(&w->d_rs[b], WR);
+    if (ok()) e = dalloc(&w->d_hs[b], WH);
+  }
+  if (ok()) e = dalloc(&w->d_static, WO * 3);
+  if (ok()) e = dalloc(&w->d_cmds, WR * 3);
+  if (ok()) e = dalloc(&w->d_mask, WR);
+  if (ok()) e = dalloc(&w->d_ranges, n_rays);
+  if (ok() && d->write_hit_idx) e = dalloc(&w->d_idx, n_rays);
+  if (ok()) e = dalloc(&w->d_fan_params, WR);
+  if (ok()) e = dalloc(&w->d_obj_lines, (size_t)w->W * w->L_obj);
+  if (ok()) e = dalloc(&w->d_pose, WR * 3);
+  if (ok()) e = dalloc(&w->d_counters, (size_t)4);
+  if (ok()) e = dalloc(&w->d_stats, (size_t)4);
+  if (ok()) e = cudaMemcpy(w->d_robots, w->robots.data(), sizeof(umrs_robot_params) * w->R, cudaMemcpyHostToDevice);
+  if (ok() && w->H) e = cudaMemcpy(w->d_humans, w->humans.data(), sizeof(umrs_human_params) * w->H, cudaMemcpyHostToDevice);
+  if (ok() && w->L_obj) e = cudaMemcpy(w->d_tmpl, tmpl.data(), sizeof(float4) * w->L_obj, cudaMemcpyHostToDevice);
+  if (ok() && w->L_obj) e = cudaMemcpy(w->d_line_ent, line_ent.data(), sizeof(int16_t) * w->L_obj, cudaMemcpyHostToDevice);
+  if (ok()) e = cudaMemcpy(w->d_ent_off, w->ent_off.data(), sizeof(int32_t) * w->ent_off.size(), cudaMemcpyHostToDevice);
+  if (ok()) e = cudaMemcpy(w->d_ray_off, w->ray_off.data(), sizeof(int32_t) * w->ray_off.size(), cudaMemcpyHostToDevice);
+  if (ok()) e = cudaMemcpy(w->d_num_rays, w->num_rays.data(), sizeof(int32_t) * w->R, cudaMemcpyHostToDevice);
+  if (ok()) e = cudaMemset(w->d_static, 0, sizeof(float) * (WO * 3 > 0 ? WO * 3 : 1));
+  if (ok()) e = cudaMemset(w->d_counters, 0, sizeof(unsigned long long) * 4);
+  if (ok()) e = cudaMemset(w->d_ranges, 0, sizeof(float) * n_rays);
+  if (!ok()) {
+    const int rc = capi_cuda_fail(e, "umrs_world_create");
+    umrs_world_destroy(w);
+    return rc;
+  }
+  *out = w;
+  // default state: robots at the origin, humans at the desc's start/goal
+  std::vector<float> zero(WR * 3, 0.f);
+  int st = umrs_world_set_robot_state(w, zero.data(), NULL);
+  if (st == UMRS_OK && w->H > 0) st = umrs_world_set_humans(w, NULL, NULL);
+  if (st != UMRS_OK) {
+    umrs_world_destroy(w);
+    *out = NULL;
+  }
+  return st;
+}
+
+int umrs_world_rays_per_world(const umrs_world* w, int32_t* n) {
+  if (w == NULL || n == NULL) return UMRS_ERR_INVALID;
+  *n = w->rays_per_world;
+  return UMRS_OK;
+}
+
+int umrs_world_object_lines_per_world(const umrs_world* w, int32_t* n) {
+  if (w == NULL || n == NULL) return UMRS_ERR_INVALID;
+  *n = w->L_obj;
+  return UMRS_OK;
+}
+
+int umrs_world_scan_header(const umrs_world* w, int32_t robot, umrs_laser_scan_header* h) {
+  if (w == NULL || h == NULL || robot < 0 || robot >= w->R) return UMRS_ERR_INVALID;
+  const umrs_laser_params& l = w->robots[robot].laser;
+  // simulator.cpp:150-159
+  h->angle_min = l.angle_min; h->angle_max = l.angle_max;
+  h->angle_increment = l.angle_increment;
+  h->time_increment = 0.0f; h->scan_time = 0.05f;
+  h->range_min = l.range_min; h->range_max = l.range_max;
+  h->num_rays = w->num_rays[robot];
+  h->ranges_offset = w->ray_off[robot];
+  return UMRS_OK;
+}
+
+int umrs_world_set_robot_state(umrs_world* w, const float* pose, const float* vel) {
+  if (w == NULL || pose == NULL) return UMRS_ERR_INVALID;
+  const size_t WR = (size_t)w->W * w->R;
+  std::vector<RobotState> s(WR);
+  memset(s.data(), 0, sizeof(RobotState) * WR);
+  for (size_t i = 0; i < WR; ++i) {
+    for (int k = 0; k < 3; ++k) {
+      s[i].pose[k] = pose[3 * i + k];
+      s[i].vel[k] = vel ? vel[3 * i + k] : 0.f;
+    }
+    // DiffDriveModel keeps its own double copies (diff_drive_model.cpp:133-139)
+    s[i].linear_vel = (double)s[i].vel[0];
+    s[i].angular_vel = (double)s[i].vel[2];
+    s[i].cmd_age = kAgeNever;  // t_last_cmd_(0)
+  }
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaMemcpy(w->d_rs[w->cur], s.data(), sizeof(RobotState) * WR, cudaMemcpyHostToDevice));
+  UMRS_CUDA(cudaMemcpy(w->d_pose, pose, sizeof(float) * WR * 3, cudaMemcpyHostToDevice));
+  return UMRS_OK;
+}
+
+int umrs_world_get_robot_state(umrs_world* w, float* pose, float* vel) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  const size_t WR = (size_t)w->W * w->R;
+  std::vector<RobotState> s(WR);
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaMemcpy(s.data(), w->d_rs[w->cur], sizeof(RobotState) * WR, cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < WR; ++i)
+    for (int k = 0; k < 3; ++k) {
+      if (pose) pose[3 * i + k] = s[i].pose[k];
+      if (vel) vel[3 * i + k] = s[i].vel[k];
+    }
+  return UMRS_OK;
+}
+
+int umrs_world_set_humans(umrs_world* w, const float* start, const float* goal) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  if (w->H == 0) return UMRS_OK;
+  const size_t WH = (size_t)w->W * w->H;
+  std::vector<HumanState> s(WH);
+  memset(s.data(), 0, sizeof(HumanState) * WH);
+  for (size_t i = 0; i < WH; ++i) {
+    const umrs_human_params& p = w->humans[i % w->H];
+    const float ds[3] = {p.start_x, p.start_y, p.start_theta};
+    const float dg[3] = {p.goal_x, p.goal_y, p.goal_theta};
+    for (int k = 0; k < 3; ++k) {
+      s[i].start[k] = start ? start[3 * i + k] : ds[k];
+      s[i].goal[k] = goal ? goal[3 * i + k] : dg[k];
+      s[i].pose[k] = s[i].start[k];  // human_object.cpp:83-84
+    }
+  }
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaMemcpy(w->d_hs[w->cur], s.data(), sizeof(HumanState) * WH, cudaMemcpyHostToDevice));
+  return UMRS_OK;
+}
+
+int umrs_world_get_human_poses(umrs_world* w, float* pose) {
+  if (w == NULL || (pose == NULL && w->H > 0)) return UMRS_ERR_INVALID;
+  const size_t WH = (size_t)w->W * w->H;
+  if (WH == 0) return UMRS_OK;
+  std::vector<HumanState> s(WH);
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaMemcpy(s.data(), w->d_hs[w->cur], sizeof(HumanState) * WH, cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < WH; ++i)
+    for (int k = 0; k < 3; ++k) pose[3 * i + k] = s[i].pose[k];
+  return UMRS_OK;
+}
+
+int umrs_world_set_static_objects(umrs_world* w, const float* pose) {
+  if (w == NULL || (pose == NULL && w->O > 0)) return UMRS_ERR_INVALID;
+  if (w->O == 0) return UMRS_OK;
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaMemcpy(w->d_static, pose, sizeof(float) * 3 * (size_t)w->W * w->O, cudaMemcpyHostToDevice));
+  return UMRS_OK;
+}
+
+int umrs_world_get_object_lines(umrs_world* w, float* segs) {
+  if (w == NULL || (segs == NULL && w->L_obj > 0)) return UMRS_ERR_INVALID;
+  if (w->L_obj == 0) return UMRS_OK;
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaMemcpy(segs, w->d_obj_lines, sizeof(float4) * (size_t)w->W * w->L_obj, cudaMemcpyDeviceToHost));
+  return UMRS_OK;
+}
+
+}  // extern "C"
+
+// ================================== stepping ========================================
+static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mask_dev,
+                        cudaStream_t stream) {
+  WorldStepParams p;
+  memset(&p, 0, sizeof(p));
+  p.c.map_segs = w->map.d_segs;
+  p.c.n_map = w->map.n;
+  p.c.ranges = w->d_ranges;
+  p.c.hit_idx = w->d_idx;
+  p.c.counters = w->counters_on ? w->d_counters : nullptr;
+  p.W = w->W; p.R = w->R; p.H = w->H; p.O = w->O;
+  p.robots = w->d_robots;
+  p.humans = w->d_humans;
+  p.tmpl = w->d_tmpl;
+  p.line_ent = w->d_line_ent;
+  p.ent_off = w->d_ent_off;
+  p.L_obj = w->L_obj;
+  p.rs_in = w->d_rs[w->cur];
+  p.rs_out = w->d_rs[w->cur ^ 1];
+  p.hs_in = w->d_hs[w->cur];
+  p.hs_out = w->d_hs[w->cur ^ 1];
+  p.static_pose = w->d_static;
+  p.cmds = cmds_dev;
+  p.cmd_mask = mask_dev;
+  p.ray_off = w->d_ray_off;
+  p.num_rays = w->d_num_rays;
+  p.rays_per_world = w->rays_per_world;
+  p.fan_params = w->d_fan_params;
+  p.obj_lines_out = w->d_obj_lines;
+  p.robot_pose_out = w->d_pose;
+  p.dt = w->desc.dt;
+  p.key0 = (uint32_t)(w->desc.seed & 0xffffffffu);
+  p.key1 = (uint32_t)(w->desc.seed >> 32);
+  p.step_lo = (uint32_t)(w->step & 0xffffffffu);
+  p.step_hi = (uint32_t)(w->step >> 32);
+  p.world_base = w->desc.world_index_base;
+  p.laser_noise = w->desc.laser_noise_enabled;
+  p.motion_noise = w->desc.motion_noise_enabled;
+  if (w->counters_on)
+    UMRS_CUDA(cudaMemsetAsync(w->d_counters, 0, sizeof(unsigned long long) * 4, stream));
+  UMRS_CUDA(launch_world_step(p, stream));
+  w->cur ^= 1;
+  w->step += 1;
+  return UMRS_OK;
+}
+
+extern "C" {
+
+int umrs_world_step_device(umrs_world* w, const float* cmds_dev, const uint8_t* mask_dev,
+                           void* stream) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  return world_launch(w, cmds_dev, mask_dev, stream ? (cudaStream_t)stream : w->stream);
+}
+
+int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
+                    float* ranges_out, int32_t* hit_idx_out) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  if (hit_idx_out != NULL && w->d_idx == NULL) return UMRS_ERR_INVALID;
+  const size_t WR = (size_t)w->W * w->R;
+  const size_t n_rays = (size_t)w->W * w->rays_per_world;
+  if (cmds)
+    UMRS_CUDA(cudaMemcpyAsync(w->d_cmds, cmds, sizeof(float) * WR * 3, cudaMemcpyHostToDevice, w->stream));
+  if (cmds && cmd_mask)
+    UMRS_CUDA(cudaMemcpyAsync(w->d_mask, cmd_mask, WR, cudaMemcpyHostToDevice, w->stream));
+  int st = world_launch(w, cmds ? w->d_cmds : nullptr, (cmds && cmd_mask) ? w->d_mask : nullptr, w->stream);
+  if (st != UMRS_OK) return st;
+  if (ranges_out)
+    UMRS_CUDA(cudaMemcpyAsync(ranges_out, w->d_ranges, sizeof(float) * n_rays, cudaMemcpyDeviceToHost, w->stream));
+  if (hit_idx_out)
+    UMRS_CUDA(cudaMemcpyAsync(hit_idx_out, w->d_idx, sizeof(int32_t) * n_rays, cudaMemcpyDeviceToHost, w->stream));
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  return UMRS_OK;
+}
+
+int umrs_world_device_buffers(umrs_world* w, float** ranges_dev, int32_t** hit_idx_dev,
+                              float** robot_pose_dev) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  if (ranges_dev) *ranges_dev = w->d_ranges;
+  if (hit_idx_dev) *hit_idx_dev = w->d_idx;
+  if (robot_pose_dev) *robot_pose_dev = w->d_pose;
+  return UMRS_OK;
+}
+
+int umrs_world_sync(umrs_world* w) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  return UMRS_OK;
+}
+
+int umrs_world_step_count(const umrs_world* w, uint64_t* steps) {
+  if (w == NULL || steps == NULL) return UMRS_ERR_INVALID;
+  *steps = w->step;
+  return UMRS_OK;
+}
+
+int umrs_world_enable_counters(umrs_world* w, int32_t on) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  w->counters_on = on != 0;
+  return UMRS_OK;
+}
+
+int umrs_world_read_counters(umrs_world* w, uint64_t* tests, uint64_t* segs, uint64_t* pairs) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  unsigned long long h[4] = {0, 0, 0, 0};
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaMemcpy(h, w->d_counters, sizeof(h), cudaMemcpyDeviceToHost));
+  if (tests) *tests = h[0];
+  if (segs) *segs = h[1];
+  if (pairs) *pairs = h[2];
+  return UMRS_OK;
+}
+
+// Fan parameters the last step actually used: [W][R][4] {loc_x, loc_y, angle_min,
+// angle_max} (world frame).  Lets a checker feed the oracle the identical fan.
+int umrs_world_get_fan_params(umrs_world* w, float* out) {
+  if (w == NULL || out == NULL) return UMRS_ERR_INVALID;
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaMemcpy(out, w->d_fan_params, sizeof(float4) * (size_t)w->W * w->R, cudaMemcpyDeviceToHost));
+  return UMRS_OK;
+}
+
+int umrs_world_stats(umrs_world* w, double* out4) {
+  if (w == NULL || out4 == NULL) return UMRS_ERR_INVALID;
+  const unsigned long long inf_bits = 0x7f800000ull;
+  double init[4] = {0.0, 0.0, 0.0, 0.0};
+  memcpy(&init[1], &inf_bits, sizeof(double));
+  UMRS_CUDA(cudaMemcpyAsync(w->d_stats, init, sizeof(init), cudaMemcpyHostToDevice, w->stream));
+  UMRS_CUDA(launch_stats(w->d_ranges, (size_t)w->W * w->rays_per_world, w->d_stats, w->stream));
+  double raw[4];
+  UMRS_CUDA(cudaMemcpyAsync(raw, w->d_stats, sizeof(raw), cudaMemcpyDeviceToHost, w->stream));
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  unsigned long long mnb, mxb;
+  memcpy(&mnb, &raw[1], 8);
+  memcpy(&mxb, &raw[2], 8);
+  const uint32_t mn32 = (uint32_t)mnb, mx32 = (uint32_t)mxb;
+  float mn, mx;
+  memcpy(&mn, &mn32, 4);
+  memcpy(&mx, &mx32, 4);
+  out4[0] = raw[0];
+  out4[1] = raw[0] > 0 ? (double)mn : 0.0;
+  out4[2] = (double)mx;
+  out4[3] = raw[3];
+  return UMRS_OK;
+}
+
+}  // extern "C"
