@@ -1,0 +1,357 @@
+#!/usr/bin/env python
+"""bench.py -- lidar rays/s (+ env-steps/s) of the fused world step on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+  torchrun ... bench.py --gpus N ...          (one rank per GPU, N > 1)
+
+Workload (BASELINE.json configs):
+  N = 1 : config 3 -- 4096 worlds x 1 Ackermann car x 1081 rays, fused step
+  N > 1 : config 5 -- 65,536 worlds sharded contiguously over the N GPUs
+against one shared seeded floor plan of --map-segments (default 1024) cleaned
+segments.  A "step" is one umrs_world_step over all worlds of the rank.
+
+Prints ONE JSON line (rank 0).  `value` = rays/s with inputs resident in HBM;
+`e2e` = the same through the host-buffer C-ABI call (pinned host buffers,
+H2D commands + D2H ranges inside the timed region).  `--impl reference` times the
+reference's own CPU scan (oracle/_ref, the unmodified vector_map.cpp) on the
+host cores instead.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_RAYS = 1081
+EXTENT = 200.0
+FLOPS_PER_TEST = 12.0  # nominal cost of one ray-segment candidate test
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4: SMs x lanes x FMA x max SM clock
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--map-segments", type=int, default=1024)
+    ap.add_argument("--worlds", type=int, default=0, help="override total worlds")
+    ap.add_argument("--cpu-sample-fans", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-flush", action="store_true")
+    return ap.parse_args()
+
+
+def total_worlds(args):
+    if args.worlds:
+        return args.worlds
+    return 4096 if args.gpus == 1 else 65536
+
+
+def workload_name(args):
+    w = total_worlds(args)
+    tag = "config3" if args.gpus == 1 else "config5"
+    return "%s: %d worlds x 1 Ackermann x %d rays, fused step+scan, floor plan %d segs" % (
+        tag, w, N_RAYS, args.map_segments)
+
+
+def make_inputs(args, rank, world_size):
+    import ut_multirobot_sim_b200 as umrs
+    from ut_multirobot_sim_b200 import synth
+    W_total = total_worlds(args)
+    per = W_total // world_size
+    base = rank * per
+    segs = umrs.map_cleanup(synth.floorplan_segments(args.map_segments, extent=EXTENT, seed=1234))
+    poses = synth.sample_free_poses_fast(segs, W_total, EXTENT, seed=11)[base:base + per]
+    cmds = [synth.ackermann_commands(W_total, 1, s, seed=42)[base:base + per] for s in range(8)]
+    return segs, poses, cmds, per, base
+
+
+class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons during the timed region (NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag = index, False
+        self.sm, self.reasons, self.sm_max = [], set(), None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.sm_max = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+            }
+            while not self.stop_flag:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    for bit, name in names.items():
+                        if r & bit:
+                            self.reasons.add(name)
+                except Exception:
+                    pass
+                time.sleep(0.01)
+        except Exception as e:  # NVML unavailable: report that, never fake a clock
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
+                "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons),
+                "samples": len(self.sm)}
+
+
+def cpu_baseline(segs, fans, range_max, n_fans, threads):
+    """oracle/_ref (the unmodified reference scan) on `threads` host cores."""
+    from tests import oracle_lib
+    ref = oracle_lib.load_ref()
+    kind = "reference"
+    if ref is None:
+        return None
+    rm = ref.map_from_segments(segs, False)
+    f = np.ascontiguousarray(fans[:n_fans], np.float32)
+    rm.scan_batch(f[:max(1, threads)], 0.4, range_max, N_RAYS, threads=threads)  # warm
+    t0 = time.perf_counter()
+    rm.scan_batch(f, 0.4, range_max, N_RAYS, threads=threads)
+    dt = time.perf_counter() - t0
+    return {"value": n_fans * N_RAYS / dt, "unit": "rays/s", "cores": threads, "kind": kind,
+            "seconds": dt}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU scan on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import ut_multirobot_sim_b200 as umrs
+    from ut_multirobot_sim_b200 import synth
+    from tests import oracle_lib
+    cores = os.cpu_count() or 1
+    segs = umrs.map_cleanup(synth.floorplan_segments(args.map_segments, extent=EXTENT, seed=1234))
+    ref = oracle_lib.load_ref()
+    if ref is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libumrs_ref.so not built"}))
+        return
+    orc = oracle_lib.load_oracle()
+    car = umrs.default_robot("ut_automata")
+    # bounded sample of the same workload: S fans per step
+    S = args.cpu_sample_fans or max(cores * 8, 256)
+    poses = synth.sample_free_poses_fast(segs, total_worlds(args), EXTENT, seed=11)[:S]
+    rm = ref.map_from_segments(segs, False)
+    import ctypes as C
+    states = [oracle_lib.RobotState() for _ in range(S)]
+    for s, p in zip(states, poses):
+        orc.lib.orc_robot_init(C.byref(s), oracle_lib._fp(np.ascontiguousarray(p, np.float32)))
+
+    def one_step(step):
+        cmds = synth.ackermann_commands(total_worlds(args), 1, step % 8, seed=42)[:S]
+        fans = np.empty((S, 4), np.float32)
+        for i, s in enumerate(states):  # restated kinematic step (ackermann_model.cpp:52-96)
+            c = np.ascontiguousarray(cmds[i, 0], np.float32)
+            orc.lib.orc_robot_command(C.byref(s), C.byref(car), oracle_lib._fp(c))
+            orc.lib.orc_robot_step(C.byref(s), C.byref(car), 0.025, 0.0, 0.0)
+            pose = np.array(list(s.pose), np.float32)
+            o = orc.laser_origin(pose, car.laser.loc_x, car.laser.loc_y)
+            fans[i] = (o[0], o[1], car.laser.angle_min + pose[2], car.laser.angle_max + pose[2])
+        return rm.scan_batch(fans, car.laser.range_min, car.laser.range_max, N_RAYS, threads=cores)
+
+    steps = min(args.steps, 20)
+    warm = min(args.warmup, 3)
+    for s in range(warm):
+        one_step(s)
+    t0 = time.perf_counter()
+    for s in range(steps):
+        one_step(warm + s)
+    dt = time.perf_counter() - t0
+    value = S * N_RAYS * steps / dt
+    sample = "%d of %d fans per step, %d steps (requested %d), all %d host threads" % (
+        S, total_worlds(args), steps, args.steps, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": "lidar_rays_per_sec", "value": value, "unit": "rays/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": dt / steps * 1e3,
+        "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args), "sample": sample},
+        "env_steps_per_sec": S * steps / dt,
+        "cpu_baseline": {"value": value, "unit": "rays/s", "cores": cores, "kind": "reference",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import ut_multirobot_sim_b200 as umrs
+    from ut_multirobot_sim_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world_size != args.gpus and world_size > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world_size))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local_rank)
+    lib = _lib.load()
+    _lib.check(lib.umrs_set_device(local_rank), "umrs_set_device")
+    if world_size > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world_size == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    segs, poses, cmd_sets, W, base = make_inputs(args, rank, world_size)
+    vmap = umrs.VectorMap(lines=segs)
+    car = umrs.default_robot("ut_automata")
+    world = umrs.World(vmap, [car], W, dt=0.025, seed=42, laser_noise=True, motion_noise=True,
+                       world_index_base=base, write_hit_idx=False)
+    world.SetPose(poses.reshape(W, 1, 3))
+    rays_per_step = W * N_RAYS
+
+    stream = torch.cuda.Stream()
+    sp = stream.cuda_stream
+    d_cmds = [torch.from_numpy(c).cuda() for c in cmd_sets]
+    flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    K, Wm = args.steps, args.warmup
+
+    def device_leg():
+        ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+        ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+        with torch.cuda.stream(stream):
+            for s in range(Wm):
+                world.step_device(d_cmds[s % 8].data_ptr(), None, sp)
+            barrier()
+            l0 = lib.umrs_kernel_launch_count()
+            for s in range(K):
+                if flush is not None:
+                    flush.zero_()          # L2 flush, outside the event pair
+                ev0[s].record(stream)
+                world.step_device(d_cmds[(Wm + s) % 8].data_ptr(), None, sp)
+                ev1[s].record(stream)
+            barrier()
+            l1 = lib.umrs_kernel_launch_count()
+        ms = sum(a.elapsed_time(b) for a, b in zip(ev0, ev1))
+        return ms, l1 - l0
+
+    def e2e_leg():
+        # host buffers (pinned), through the public host-buffer C-ABI call
+        h_cmds = [torch.from_numpy(c).pin_memory() for c in cmd_sets]
+        h_ranges = torch.empty((W, N_RAYS), dtype=torch.float32).pin_memory()
+        for s in range(min(Wm, 3)):
+            world.step_raw(h_cmds[s % 8].data_ptr(), None, h_ranges.data_ptr(), None)
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(K):
+            world.step_raw(h_cmds[s % 8].data_ptr(), None, h_ranges.data_ptr(), None)
+        barrier()
+        dt = time.perf_counter() - t0
+        chk = float(h_ranges[0, :8].sum())
+        return dt * 1e3, h_cmds[0].numel() * 4, h_ranges.numel() * 4, chk
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms_dev, launches = device_leg()
+    clocks = sampler.result()
+    ms_dev = max_over_ranks(ms_dev)
+    ms_e2e, h2d, d2h, _ = e2e_leg()
+    ms_e2e = max_over_ranks(ms_e2e)
+
+    # work accounting for the roofline: one untimed step with device counters on
+    world.enable_counters(True)
+    world.step_device(d_cmds[0].data_ptr(), None, sp)
+    cnt = world.read_counters()
+    world.enable_counters(False)
+    stats = world.stats()
+
+    total_rays = rays_per_step * world_size
+    value = total_rays * K / (ms_dev * 1e-3)
+    e2e_value = total_rays * K / (ms_e2e * 1e-3)
+    tests = cnt["ray_seg_tests"]
+    kernel_s = ms_dev * 1e-3 / K
+    achieved_tflops = FLOPS_PER_TEST * tests / kernel_s / 1e12
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    alg_bytes = rays_per_step * 4 + W * (64 * 2 + 12 + 16 + 12)  # ranges out + state r/w + cmd + fan + pose
+    out = {
+        "metric": "lidar_rays_per_sec", "value": value, "unit": "rays/s",
+        "n_gpus": world_size, "steps": K, "warmup": Wm, "ms_per_step": ms_dev / K,
+        "higher_is_better": True, "scaling": "strong" if world_size > 1 else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args), "worlds_per_gpu": W,
+                   "map_segments": int(len(segs)), "laser_noise": True, "motion_noise": True,
+                   "l2": "none" if flush is None else "flushed between timed steps (256 MiB memset outside the event pairs)",
+                   "timing": "sum of per-step CUDA-event pairs on the launch stream, max over ranks"},
+        "env_steps_per_sec": W * world_size * K / (ms_dev * 1e-3),
+        "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K,
+                "env_steps_per_sec": W * world_size * K / (ms_e2e * 1e-3)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": FP32_PEAK_TFLOPS,
+                     "unit": "TFLOP/s", "frac": achieved_tflops / FP32_PEAK_TFLOPS, "traffic": None,
+                     "kernel": "k1_world_step", "tests_per_launch": int(tests),
+                     "tests_per_ray": tests / rays_per_step,
+                     "segs_prepared_per_fan": cnt["segs_prepared"] / W,
+                     "flops_per_test": FLOPS_PER_TEST,
+                     "peak_source": "nominal FP32 pipe: 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json has no FP32 figure)",
+                     "hbm": {"achieved_gbs": alg_bytes / kernel_s / 1e9, "peak_gbs": hbm_peak,
+                             "frac": alg_bytes / kernel_s / 1e9 / hbm_peak,
+                             "peak_source": "measured" if "hbm_gbs" in peaks else "fallback"}},
+        "stats": stats,
+    }
+    if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
+        fans = world.fan_params().reshape(-1, 4)
+        cores = os.cpu_count() or 1
+        n_fans = args.cpu_sample_fans or min(W, max(cores * 16, 512))
+        cb = cpu_baseline(segs, fans, car.laser.range_max, n_fans, cores)
+        if cb is not None:
+            one = cpu_baseline(segs, fans, car.laser.range_max, min(n_fans, 64), 1)
+            cb["sample"] = "%d of %d fans of the same step, reference GetPredictedScan, %d threads" % (
+                n_fans, W, cores)
+            cb["single_thread_value"] = one["value"]
+            out["cpu_baseline"] = cb
+    if rank == 0:
+        print(json.dumps(out))
+    if world_size > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

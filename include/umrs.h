@@ -54,6 +54,13 @@ const char* umrs_last_cuda_error(void);
 /* Number of kernels THIS LIBRARY has launched since load (all handles). */
 uint64_t umrs_kernel_launch_count(void);
 
+/* Device selection for the calling thread (cudaSetDevice inside the library's
+ * own CUDA runtime instance); handles created afterwards live on that device.
+ * One process per GPU is the intended deployment. */
+int umrs_set_device(int32_t device);
+int umrs_get_device(int32_t* device);
+int umrs_device_count(int32_t* count);
+
 /* ---- parameter PODs (host shell fills them from its parsed Lua config) ----- */
 
 /* Robot model kinds; strings as in simulator.cpp:128-142 / sim_config.lua:51-55. */

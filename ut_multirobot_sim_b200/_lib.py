@@ -74,6 +74,9 @@ SIGNATURES = {
     "umrs_status_string": (C.c_char_p, [C.c_int]),
     "umrs_last_cuda_error": (C.c_char_p, []),
     "umrs_kernel_launch_count": (C.c_uint64, []),
+    "umrs_set_device": (C.c_int, [C.c_int32]),
+    "umrs_get_device": (C.c_int, [_I]),
+    "umrs_device_count": (C.c_int, [_I]),
     "umrs_model_type_from_string": (C.c_int, [C.c_char_p]),
     "umrs_laser_num_rays": (C.c_int, [C.POINTER(LaserParams)]),
     "umrs_default_laser": (None, [C.POINTER(LaserParams)]),

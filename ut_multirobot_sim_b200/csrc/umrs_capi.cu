@@ -127,6 +127,29 @@ extern "C" {
 const char* umrs_last_cuda_error(void) { return g_last_cuda_error.c_str(); }
 uint64_t umrs_kernel_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
+int umrs_set_device(int32_t device) {
+  UMRS_CUDA(cudaSetDevice(device));
+  return UMRS_OK;
+}
+int umrs_get_device(int32_t* device) {
+  if (device == NULL) return UMRS_ERR_INVALID;
+  int d = 0;
+  UMRS_CUDA(cudaGetDevice(&d));
+  *device = d;
+  return UMRS_OK;
+}
+int umrs_device_count(int32_t* count) {
+  if (count == NULL) return UMRS_ERR_INVALID;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  *count = n;
+  return UMRS_OK;
+}
+
 int umrs_map_create(const float* segs_xyxy, int32_t n, umrs_map** out) {
   if (out == NULL || n < 0 || (n > 0 && segs_xyxy == NULL)) return UMRS_ERR_INVALID;
   *out = NULL;

@@ -249,7 +249,7 @@ int umrs_world_set_robot_state(umrs_world* w, const float* pose, const float* ve
     s[i].angular_vel = (double)s[i].vel[2];
     s[i].cmd_age = kAgeNever;  // t_last_cmd_(0)
   }
-  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaDeviceSynchronize());
   UMRS_CUDA(cudaMemcpy(w->d_rs[w->cur], s.data(), sizeof(RobotState) * WR, cudaMemcpyHostToDevice));
   UMRS_CUDA(cudaMemcpy(w->d_pose, pose, sizeof(float) * WR * 3, cudaMemcpyHostToDevice));
   return UMRS_OK;
@@ -259,7 +259,7 @@ int umrs_world_get_robot_state(umrs_world* w, float* pose, float* vel) {
   if (w == NULL) return UMRS_ERR_INVALID;
   const size_t WR = (size_t)w->W * w->R;
   std::vector<RobotState> s(WR);
-  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaDeviceSynchronize());
   UMRS_CUDA(cudaMemcpy(s.data(), w->d_rs[w->cur], sizeof(RobotState) * WR, cudaMemcpyDeviceToHost));
   for (size_t i = 0; i < WR; ++i)
     for (int k = 0; k < 3; ++k) {
@@ -285,7 +285,7 @@ int umrs_world_set_humans(umrs_world* w, const float* start, const float* goal) 
       s[i].pose[k] = s[i].start[k];  // human_object.cpp:83-84
     }
   }
-  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaDeviceSynchronize());
   UMRS_CUDA(cudaMemcpy(w->d_hs[w->cur], s.data(), sizeof(HumanState) * WH, cudaMemcpyHostToDevice));
   return UMRS_OK;
 }
@@ -295,7 +295,7 @@ int umrs_world_get_human_poses(umrs_world* w, float* pose) {
   const size_t WH = (size_t)w->W * w->H;
   if (WH == 0) return UMRS_OK;
   std::vector<HumanState> s(WH);
-  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaDeviceSynchronize());
   UMRS_CUDA(cudaMemcpy(s.data(), w->d_hs[w->cur], sizeof(HumanState) * WH, cudaMemcpyDeviceToHost));
   for (size_t i = 0; i < WH; ++i)
     for (int k = 0; k < 3; ++k) pose[3 * i + k] = s[i].pose[k];
@@ -305,7 +305,7 @@ int umrs_world_get_human_poses(umrs_world* w, float* pose) {
 int umrs_world_set_static_objects(umrs_world* w, const float* pose) {
   if (w == NULL || (pose == NULL && w->O > 0)) return UMRS_ERR_INVALID;
   if (w->O == 0) return UMRS_OK;
-  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaDeviceSynchronize());
   UMRS_CUDA(cudaMemcpy(w->d_static, pose, sizeof(float) * 3 * (size_t)w->W * w->O, cudaMemcpyHostToDevice));
   return UMRS_OK;
 }
@@ -313,7 +313,7 @@ int umrs_world_set_static_objects(umrs_world* w, const float* pose) {
 int umrs_world_get_object_lines(umrs_world* w, float* segs) {
   if (w == NULL || (segs == NULL && w->L_obj > 0)) return UMRS_ERR_INVALID;
   if (w->L_obj == 0) return UMRS_OK;
-  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaDeviceSynchronize());
   UMRS_CUDA(cudaMemcpy(segs, w->d_obj_lines, sizeof(float4) * (size_t)w->W * w->L_obj, cudaMemcpyDeviceToHost));
   return UMRS_OK;
 }
@@ -424,7 +424,7 @@ int umrs_world_enable_counters(umrs_world* w, int32_t on) {
 int umrs_world_read_counters(umrs_world* w, uint64_t* tests, uint64_t* segs, uint64_t* pairs) {
   if (w == NULL) return UMRS_ERR_INVALID;
   unsigned long long h[4] = {0, 0, 0, 0};
-  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaDeviceSynchronize());  // the step may have run on a caller stream
   UMRS_CUDA(cudaMemcpy(h, w->d_counters, sizeof(h), cudaMemcpyDeviceToHost));
   if (tests) *tests = h[0];
   if (segs) *segs = h[1];
@@ -436,7 +436,7 @@ int umrs_world_read_counters(umrs_world* w, uint64_t* tests, uint64_t* segs, uin
 // angle_max} (world frame).  Lets a checker feed the oracle the identical fan.
 int umrs_world_get_fan_params(umrs_world* w, float* out) {
   if (w == NULL || out == NULL) return UMRS_ERR_INVALID;
-  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaDeviceSynchronize());
   UMRS_CUDA(cudaMemcpy(out, w->d_fan_params, sizeof(float4) * (size_t)w->W * w->R, cudaMemcpyDeviceToHost));
   return UMRS_OK;
 }
@@ -446,6 +446,7 @@ int umrs_world_stats(umrs_world* w, double* out4) {
   const unsigned long long inf_bits = 0x7f800000ull;
   double init[4] = {0.0, 0.0, 0.0, 0.0};
   memcpy(&init[1], &inf_bits, sizeof(double));
+  UMRS_CUDA(cudaDeviceSynchronize());  // the last step may have run on a caller stream
   UMRS_CUDA(cudaMemcpyAsync(w->d_stats, init, sizeof(init), cudaMemcpyHostToDevice, w->stream));
   UMRS_CUDA(launch_stats(w->d_ranges, (size_t)w->W * w->rays_per_world, w->d_stats, w->stream));
   double raw[4];
