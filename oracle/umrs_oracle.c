@@ -206,6 +206,12 @@ static int seg_intersection(const float l[4], const float m[4], float out[2]) {
   return 1;
 }
 
+int32_t orc_line_intersection(const float a[4], const float b[4], float out[2]) {
+  out[0] = 0.0f;
+  out[1] = 0.0f;
+  return seg_intersection(a, b, out);
+}
+
 static void seg_dir(const float l[4], float d[2]) { /* line2d.h:62-64 */
   float dx = l[2] - l[0], dy = l[3] - l[1];
   const float z = dx * dx + dy * dy;

@@ -57,6 +57,10 @@ void orc_laser_origin(const float pose_xyt[3], float laser_x, float laser_y,
 /* ---- map cleanup (vector_map.cpp:359-395) --------------------------------- */
 int32_t orc_map_cleanup(const float* in_xyxy, int32_t n, float* out_xyxy, int32_t cap);
 
+/* Line<float>::Intersection (line2d.h:139-160), the predicate Cleanup splits
+ * with: returns 1 and the crossing point of segments a and b, else 0. */
+int32_t orc_line_intersection(const float a_xyxy[4], const float b_xyxy[4], float out_xy[2]);
+
 /* ---- kinematic steps ---------------------------------------------------------- */
 typedef struct orc_robot_state {
   float pose[3];      /* pose_  {x, y, angle}         entity_base.h:36 */

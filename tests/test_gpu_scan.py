@@ -1,0 +1,205 @@
+"""GPU parity of the scan path (K1 / K2) through the C-ABI, against the tier-B
+oracle, the committed golden vectors of the reference (tier A), and
+size-independent properties at BASELINE.json's full sizes.
+
+Tolerances (BASELINE.json north_star): per-ray range within 1e-5 relative of the
+oracle; hit-segment index identical except at certified ties (two candidates
+whose ranges at that ray agree within 1e-5 relative; the lowest index wins in
+the oracle).
+"""
+import ctypes as C
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import ut_multirobot_sim_b200 as umrs
+from ut_multirobot_sim_b200 import _lib, synth
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SCAN_GOLDEN = sorted(g for g in glob.glob(os.path.join(HERE, "golden", "*.npz"))
+                     if "primitives" not in g)
+REL_TOL = 1e-5
+
+
+def _load(path):
+    d = np.load(path)
+    return {k: d[k] for k in d.files}
+
+
+def check_against_tierb(oracle, segs, obj, fan, range_max, n, r_gpu, i_gpu, skip=(0, 0)):
+    """Returns (#rays bit-identical, #certified ties); asserts the contract."""
+    r_o, i_o = oracle.scan_tierb(segs, obj, fan[:2], range_max, fan[2], fan[3], n, skip=skip)
+    rel = np.abs(r_gpu.astype(np.float64) - r_o) / np.maximum(np.abs(r_o.astype(np.float64)), 1e-9)
+    assert rel.max() <= REL_TOL, "range off by %.3g rel at ray %d" % (rel.max(), rel.argmax())
+    ties = 0
+    allseg = np.concatenate([np.asarray(segs, np.float32).reshape(-1, 4),
+                             np.asarray(obj if obj is not None else np.zeros((0, 4)), np.float32).reshape(-1, 4)])
+    for k in np.nonzero(i_gpu != i_o)[0]:
+        assert i_gpu[k] >= 0 and i_o[k] >= 0, "hit/no-hit disagreement at ray %d" % k
+        ra = oracle.candidate_range(allseg[i_gpu[k]], fan[:2], fan[2], fan[3], n, int(k))
+        assert np.isfinite(ra) and abs(ra - r_o[k]) <= REL_TOL * abs(r_o[k]), \
+            "idx mismatch at ray %d is not a tie: %r vs %r" % (k, ra, r_o[k])
+        ties += 1
+    return int((r_gpu.view(np.uint32) == r_o.view(np.uint32)).sum()), ties
+
+
+@pytest.mark.parametrize("path", SCAN_GOLDEN, ids=[os.path.basename(p) for p in SCAN_GOLDEN])
+def test_predicted_scan_matches_golden(oracle, path):
+    """Drop-in umrs_predicted_scan (VectorMap::GetPredictedScan's argument list) on
+    the committed fixtures: tier B within tolerance + exact idx; every ray that
+    disagrees with the reference's own output (tier A) is one where tier B
+    disagrees with it too (SURVEY.md 8c exception classes D1-D6)."""
+    g = _load(path)
+    n, rmax = int(g["num_rays"]), float(g["range_max"])
+    vmap = umrs.VectorMap(lines=g["raw"], cleaned=False)
+    assert np.array_equal(vmap.lines.view(np.uint32), g["segs"].view(np.uint32))
+    vmap.object_lines = g["obj"]
+    exact = total = 0
+    for f, ra, rb, ib in zip(g["fans"], g["tier_a"], g["tier_b"], g["idx_b"]):
+        r, i = vmap.GetPredictedScan(f[:2], 0.4, rmax, f[2], f[3], n, return_index=True)
+        e, _ = check_against_tierb(oracle, g["segs"], g["obj"], f, rmax, n, r, i)
+        exact += e
+        total += n
+        rel_b = np.abs(r - rb) / np.maximum(np.abs(rb), 1e-9)
+        assert rel_b.max() <= REL_TOL
+        rel_a = np.abs(r.astype(np.float64) - ra) / np.maximum(np.abs(ra), 1e-9)
+        rel_ab = np.abs(rb.astype(np.float64) - ra) / np.maximum(np.abs(ra), 1e-9)
+        # GPU-vs-reference disagreements are a subset of tierB-vs-reference ones
+        # (2e-5 on the left so a ray sitting at the threshold cannot flip sides)
+        assert not np.any((rel_a > 2e-5) & (rel_ab <= 1e-5))
+    assert exact / total > 0.999, "only %.4f of rays bit-identical to the oracle" % (exact / total)
+
+
+def test_scan_batch_equals_single_scans(oracle):
+    g = _load(os.path.join(HERE, "golden", "floorplan_256.npz"))
+    n, rmax = int(g["num_rays"]), float(g["range_max"])
+    vmap = umrs.VectorMap(lines=g["segs"])
+    rb, ib = vmap.ScanBatch(g["fans"], rmax, n, return_index=True)
+    for k, f in enumerate(g["fans"]):
+        r, i = vmap.GetPredictedScan(f[:2], 0.4, rmax, f[2], f[3], n, return_index=True)
+        assert np.array_equal(r.view(np.uint32), rb[k].view(np.uint32))
+        assert np.array_equal(i, ib[k])
+
+
+def test_empty_map_and_edge_sizes(oracle):
+    """Empty candidate set -> every ray keeps the fill value range_max
+    (vector_map.cpp:433); num_rays == 1; zero fans; hits beyond range_max inside
+    the AABB are returned unclamped (class D7)."""
+    vmap = umrs.VectorMap(lines=np.zeros((0, 4), np.float32))
+    r, i = vmap.GetPredictedScan((0, 0), 0.4, 10.0, -1.0, 1.0, 7, return_index=True)
+    assert np.all(r == np.float32(10.0)) and np.all(i == -1)
+    assert vmap.ScanBatch(np.zeros((0, 4), np.float32), 10.0, 5).shape == (0, 5)
+    # one wall at x = 9.9, seen from the origin with range_max 10: the corner
+    # rays hit it beyond 10 m and are NOT clamped
+    wall = np.array([[9.9, -9.9, 9.9, 9.9]], np.float32)
+    vmap = umrs.VectorMap(lines=wall)
+    r, i = vmap.GetPredictedScan((0, 0), 0.4, 10.0, -0.7, 0.7, 64, return_index=True)
+    check_against_tierb(oracle, wall, None, np.array([0, 0, -0.7, 0.7], np.float32), 10.0, 64, r, i)
+    assert r.max() > 10.0 and np.all(i == 0)
+    r1 = vmap.GetPredictedScan((0, 0), 0.4, 10.0, 0.0, 0.1, 1)
+    assert r1.shape == (1,) and r1[0] == np.float32(9.9)
+    # AABB cull: a wall just outside [loc +- range_max]^2 is not a candidate
+    far = np.array([[10.5, -1, 10.5, 1]], np.float32)
+    r = umrs.VectorMap(lines=far).GetPredictedScan((0, 0), 0.4, 10.0, -0.5, 0.5, 9)
+    assert np.all(r == np.float32(10.0))
+
+
+def test_wraparound_and_full_circle_fans(oracle):
+    """Segments straddling the -x axis (a0 > a1 after the swap) and fans whose
+    world-frame limits exceed +-pi (angle_min + theta), incl. the 360 deg jackal."""
+    rng = np.random.default_rng(2)
+    segs = umrs.map_cleanup(synth.floorplan_segments(128, extent=60.0, seed=8))
+    vmap = umrs.VectorMap(lines=segs)
+    poses = synth.sample_free_poses(segs, 12, 60.0, seed=3)
+    for p in poses:
+        for amin, amax, n in ((-2.356, 2.356, 1081), (-np.pi, np.pi, 3601), (-0.3, 0.2, 33)):
+            th = rng.uniform(-7, 7)  # un-normalised heading
+            f = np.array([p[0], p[1], np.float32(amin) + np.float32(th), np.float32(amax) + np.float32(th)], np.float32)
+            r, i = vmap.GetPredictedScan(f[:2], 0.4, 100.0, f[2], f[3], n, return_index=True)
+            check_against_tierb(oracle, segs, None, f, 100.0, n, r, i)
+
+
+def test_ties_resolve_to_lowest_index(oracle):
+    """Two identical walls: the oracle keeps the first (strict <); so must the GPU."""
+    segs = np.array([[5, -3, 5, 3], [5, -3, 5, 3], [7, -3, 7, 3]], np.float32)
+    vmap = umrs.VectorMap(lines=segs)
+    r, i = vmap.GetPredictedScan((0, 0), 0.4, 50.0, -0.4, 0.4, 101, return_index=True)
+    assert np.all(i == 0)
+    check_against_tierb(oracle, segs, None, np.array([0, 0, -0.4, 0.4], np.float32), 50.0, 101, r, i)
+
+
+def test_object_lines_occlude(oracle):
+    g = _load(os.path.join(HERE, "golden", "clutter_objects.npz"))
+    n, rmax = int(g["num_rays"]), float(g["range_max"])
+    vmap = umrs.VectorMap(lines=g["segs"])
+    f = g["fans"][0]
+    r0, i0 = vmap.GetPredictedScan(f[:2], 0.4, rmax, f[2], f[3], n, return_index=True)
+    vmap.object_lines = g["obj"]
+    r1, i1 = vmap.GetPredictedScan(f[:2], 0.4, rmax, f[2], f[3], n, return_index=True)
+    assert np.all(r1 <= r0)
+    assert np.all(i0 < len(g["segs"]))
+    hits_obj = i1 >= len(g["segs"])
+    assert np.array_equal(r1[~hits_obj].view(np.uint32), r0[~hits_obj].view(np.uint32))
+
+
+def test_invalid_arguments_return_status():
+    lib = _lib.load()
+    vmap = umrs.VectorMap(lines=np.array([[0, 0, 1, 0]], np.float32))
+    out = np.zeros(4, np.float32)
+    fp = out.ctypes.data_as(C.POINTER(C.c_float))
+    assert lib.umrs_predicted_scan(None, None, 0, 0, 0, 0.4, 10, -1, 1, 4, fp, None) == _lib.ERR_INVALID
+    assert lib.umrs_predicted_scan(vmap._h, None, 0, 0, 0, 0.4, 10, -1, 1, 0, fp, None) == _lib.ERR_INVALID
+    assert lib.umrs_predicted_scan(vmap._h, None, 0, 0, 0, 0.4, 10, -1, 1, 4, None, None) == _lib.ERR_INVALID
+    assert lib.umrs_predicted_scan(vmap._h, None, 3, 0, 0, 0.4, 10, -1, 1, 4, fp, None) == _lib.ERR_INVALID
+    assert lib.umrs_map_create(None, 5, C.byref(C.c_void_p())) == _lib.ERR_INVALID
+
+
+def test_map_load_file_roundtrip(tmp_path, oracle):
+    """VectorMap::Load: text format + Cleanup (vector_map.cpp:397-411)."""
+    raw = synth.floorplan_segments(64, extent=50.0, seed=4)
+    path = tmp_path / "m.vectormap.txt"
+    synth.write_map(str(path), raw)
+    vmap = umrs.VectorMap(file=str(path))
+    assert np.array_equal(vmap.lines.view(np.uint32), oracle.map_cleanup(raw).view(np.uint32))
+
+
+@pytest.mark.parametrize("kernel", [0, 1], ids=["k1_smem", "k2_grid"])
+def test_forced_kernels_agree(oracle, kernel):
+    """The shared-memory kernel and the uniform-grid walk are the same function."""
+    lib = _lib.load()
+    g = _load(os.path.join(HERE, "golden", "floorplan_1024.npz"))
+    n, rmax = int(g["num_rays"]), float(g["range_max"])
+    vmap = umrs.VectorMap(lines=g["segs"])
+    _lib.check(lib.umrs_map_set_scan_kernel(vmap._h, kernel), "set_scan_kernel")
+    r, i = vmap.ScanBatch(g["fans"], rmax, n, return_index=True)
+    for k, f in enumerate(g["fans"]):
+        check_against_tierb(oracle, g["segs"], None, f, rmax, n, r[k], i[k])
+
+
+def test_large_map_grid_walk(oracle):
+    """BASELINE config 4 (scaled for the checker): 100k-segment city-block map, the
+    candidate set does not fit shared memory -> uniform-grid kernel.  Full tier-B
+    check on 8 fans; properties on 925 fans x 1081 rays (~1M rays)."""
+    segs = synth.cityblock_segments(100000, extent=2000.0, seed=99)
+    vmap = umrs.VectorMap(lines=segs)  # blocks never touch: already "clean"
+    rng = np.random.default_rng(4)
+    n_fans, n = 925, 1081
+    poses = np.stack([rng.uniform(100, 1900, n_fans), rng.uniform(100, 1900, n_fans),
+                      rng.uniform(-np.pi, np.pi, n_fans)], 1).astype(np.float32)
+    d135 = np.float32(np.pi * 135.0 / 180.0)
+    fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - d135, poses[:, 2] + d135], 1).astype(np.float32)
+    r, i = vmap.ScanBatch(fans, 100.0, n, return_index=True)
+    assert r.shape == (n_fans, n)
+    for k in range(8):
+        check_against_tierb(oracle, segs, None, fans[k], 100.0, n, r[k], i[k])
+    # properties over the full 1M rays: finite, positive, bounded by the AABB corner;
+    # no-hit rays carry exactly range_max; idx in range
+    assert np.isfinite(r).all() and (r > 0).all() and r.max() <= 100.0 * np.sqrt(2) * (1 + 1e-5)
+    assert np.all(r[i < 0] == np.float32(100.0)) and i.max() < len(segs)
+    # determinism
+    r2 = vmap.ScanBatch(fans, 100.0, n)
+    assert np.array_equal(r.view(np.uint32), r2.view(np.uint32))
