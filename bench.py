@@ -318,7 +318,7 @@ def run_b200(args):
         "clocks": clocks,
         "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": FP32_PEAK_TFLOPS,
                      "unit": "TFLOP/s", "frac": achieved_tflops / FP32_PEAK_TFLOPS, "traffic": None,
-                     "kernel": "k1_world_step", "tests_per_launch": int(tests),
+                     "kernel": "k_world_step", "tests_per_launch": int(tests),
                      "tests_per_ray": tests / rays_per_step,
                      "segs_prepared_per_fan": cnt["segs_prepared"] / W,
                      "flops_per_test": FLOPS_PER_TEST,

@@ -618,11 +618,11 @@ void orc_philox4x32(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4
 }
 
 void orc_box_muller(uint32_t u0, uint32_t u1, float out[2]) {
-  /* u in (0,1): (top 24 bits + 0.5) * 2^-24 */
+  /* u in (0,1): (top 24 bits + 0.5) * 2^-24; angle 2*pi*y - pi in (-pi, pi) */
   const float x = ((float)(u0 >> 8) + 0.5f) * (1.0f / 16777216.0f);
   const float y = ((float)(u1 >> 8) + 0.5f) * (1.0f / 16777216.0f);
   const float r = sqrtf(-2.0f * logf(x));
-  const float th = 6.28318530717958647692f * y;
+  const float th = 6.28318530717958647692f * y - 3.14159265358979323846f;
   out[0] = r * cosf(th);
   out[1] = r * sinf(th);
 }

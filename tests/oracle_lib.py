@@ -242,7 +242,8 @@ def load_oracle():
     global _oracle
     if _oracle is None:
         p = os.path.join(ORACLE_DIR, "liboracle.so")
-        if not os.path.exists(p):
+        srcs = [os.path.join(ORACLE_DIR, f) for f in ("umrs_oracle.c", "umrs_oracle.h")]
+        if not os.path.exists(p) or any(os.path.getmtime(f) > os.path.getmtime(p) for f in srcs):
             build()
         _oracle = Oracle(C.CDLL(p))
     return _oracle

@@ -203,3 +203,54 @@ def test_large_map_grid_walk(oracle):
     # determinism
     r2 = vmap.ScanBatch(fans, 100.0, n)
     assert np.array_equal(r.view(np.uint32), r2.view(np.uint32))
+
+
+@pytest.mark.parametrize("kernel", [0, 1], ids=["k1_smem", "k2_grid"])
+def test_multipass_when_candidates_exceed_the_slots(oracle, monkeypatch, kernel):
+    """UMRS_CAP bounds the shared-memory candidate slots per pass: with 96 slots a
+    1024-segment fan takes ~11 passes; results (incl. ties across passes and the
+    object lines, which live in the last source row) must not change."""
+    lib = _lib.load()
+    monkeypatch.setenv("UMRS_CAP", "96")
+    g = _load(os.path.join(HERE, "golden", "clutter_objects.npz"))
+    n, rmax = int(g["num_rays"]), float(g["range_max"])
+    vmap = umrs.VectorMap(lines=g["segs"])
+    vmap.object_lines = g["obj"]
+    _lib.check(lib.umrs_map_set_scan_kernel(vmap._h, kernel), "set_scan_kernel")
+    r, i = vmap.ScanBatch(g["fans"], rmax, n, return_index=True)
+    for k, f in enumerate(g["fans"]):
+        check_against_tierb(oracle, g["segs"], g["obj"], f, rmax, n, r[k], i[k])
+    monkeypatch.delenv("UMRS_CAP")
+    r1, i1 = vmap.ScanBatch(g["fans"], rmax, n, return_index=True)
+    assert np.array_equal(r.view(np.uint32), r1.view(np.uint32)) and np.array_equal(i, i1)
+    # duplicates split across passes still resolve to the lowest index
+    monkeypatch.setenv("UMRS_CAP", "32")
+    segs = np.array([[5, -3, 5, 3]] * 70 + [[7, -3, 7, 3]], np.float32)
+    vm2 = umrs.VectorMap(lines=segs)
+    _lib.check(lib.umrs_map_set_scan_kernel(vm2._h, kernel), "set_scan_kernel")
+    r2, i2 = vm2.GetPredictedScan((0, 0), 0.4, 50.0, -0.4, 0.4, 101, return_index=True)
+    assert np.all(i2 == 0)
+
+
+def test_grid_kernel_with_long_segments_and_far_poses(oracle):
+    """K2 corner cases: segments longer than two cells (always-visited tail), fans
+    outside the map's bounding box, fans that see nothing."""
+    lib = _lib.load()
+    rng = np.random.default_rng(12)
+    blocks = synth.cityblock_segments(6000, extent=400.0, seed=5)
+    longs = np.array([[0, 0, 400, 0], [400, 0, 400, 400], [400, 400, 0, 400], [0, 400, 0, 0],
+                      [10, 200, 390, 203]], np.float32)
+    segs = np.concatenate([longs, blocks]).astype(np.float32)
+    vmap = umrs.VectorMap(lines=segs)
+    _lib.check(lib.umrs_map_set_scan_kernel(vmap._h, 1), "set_scan_kernel")
+    fans = []
+    for _ in range(10):
+        x, y, th = rng.uniform(5, 395), rng.uniform(5, 395), rng.uniform(-3, 3)
+        fans.append([x, y, th - 2.356, th + 2.356])
+    fans += [[-50, -50, 0.0, 1.5], [450, 200, 2.0, 4.0], [200, -30, 0.5, 2.5], [5000, 5000, 0, 1]]
+    fans = np.array(fans, np.float32)
+    r, i = vmap.ScanBatch(fans, 60.0, 541, return_index=True)
+    for k, f in enumerate(fans):
+        check_against_tierb(oracle, segs, None, f, 60.0, 541, r[k], i[k])
+    assert np.all(r[-1] == np.float32(60.0)) and np.all(i[-1] == -1)
+    assert (i[:10] < 5).any() and (i[:10] >= 5).any()   # both long walls and blocks are hit

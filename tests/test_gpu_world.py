@@ -70,10 +70,17 @@ def test_kinematic_step_parity(oracle, kind):
             _oracle_step(oracle, states[w], rp, cmds[w, 0] if mask[w, 0] else None)
             op = np.array(list(states[w].pose), np.float64)
             ov = np.array(list(states[w].vel), np.float64)
+            # the omni model stores non-finite commands (omnidirectional_model.cpp:49-58
+            # only prints): NaN then propagates identically on both sides
+            assert np.array_equal(np.isnan(gp[w, 0]), np.isnan(op)), (kind, step, w, gp[w, 0], op)
+            assert np.array_equal(np.isnan(gv[w, 0]), np.isnan(ov)), (kind, step, w, gv[w, 0], ov)
+            fin = ~np.isnan(op)
             tol = 1e-4 * (1 + np.abs(op))
-            assert np.all(np.abs(gp[w, 0] - op) <= tol), (kind, step, w, gp[w, 0], op)
-            assert np.all(np.abs(gv[w, 0] - ov) <= 1e-5 * (1 + np.abs(ov))), (kind, step, w, gv[w, 0], ov)
-            worst_step = max(worst_step, float(np.max(np.abs(gp[w, 0] - op))))
+            assert np.all(np.abs(gp[w, 0] - op)[fin] <= tol[fin]), (kind, step, w, gp[w, 0], op)
+            fv = ~np.isnan(ov)
+            assert np.all(np.abs(gv[w, 0] - ov)[fv] <= (1e-5 * (1 + np.abs(ov)))[fv]), (kind, step, w, gv[w, 0], ov)
+            if fin.all():
+                worst_step = max(worst_step, float(np.max(np.abs(gp[w, 0] - op))))
     assert worst_step < 1e-4
 
 
@@ -290,12 +297,15 @@ def test_laser_noise_dropout_rule_and_distribution(oracle):
 
 
 def test_noise_is_the_documented_philox_stream(oracle):
-    """out = max(0, r + sigma * g) with g from Philox4x32-10(counter = {ray/4,
-    global fan, step_lo, step_hi ^ 'LASR'}, key = seed) + Box-Muller, restated on
-    the host by the oracle."""
+    """out = max(0, r + sigma * g): ray i = 128*s + 32*q + l takes normal q of
+    Philox4x32-10(counter = {32*s + l, global fan, step_lo, step_hi ^ 'LASR'},
+    key = seed) + Box-Muller, restated on the host by the oracle.  The kernel uses
+    the hardware log/sin/cos approximations (abs. error ~4e-7 in g, 4e-9 m in the
+    range): tolerance 2e-6 * (1 + |range|)."""
     W = 4
     clean_w, segs, car, _ = _make_car_world(W, M=64, noise=False)
-    noisy_w, _, _, _ = _make_car_world(W, M=64, noise=True, seed=0x1234567800000042, base=7)
+    noisy_w, _, _, _ = _make_car_world(W, M=64, noise=True, seed=0x1234567800000042, base=7, total=7 + W)
+    clean_w.SetPose(noisy_w.GetPose()[0])
     cmds = np.zeros((W, 1, 3), np.float32)
     clean = clean_w.Step(cmds)
     noisy = noisy_w.Step(cmds)
@@ -304,9 +314,10 @@ def test_noise_is_the_documented_philox_stream(oracle):
         for i in (0, 1, 2, 3, 4, 517, 1080):
             if float(clean[w, i]) > float(np.float32(100.0)) - 0.1:
                 continue
-            words = oracle.philox([i >> 2, 7 + w, 0, 0 ^ 0x4C415352], [0x00000042, 0x12345678])
-            pair = oracle.box_muller(words[2], words[3]) if (i & 2) else oracle.box_muller(words[0], words[1])
-            g = pair[1] if (i & 1) else pair[0]
+            blk, q = 32 * (i >> 7) + (i & 31), (i >> 5) & 3
+            words = oracle.philox([blk, 7 + w, 0, 0 ^ 0x4C415352], [0x00000042, 0x12345678])
+            pair = oracle.box_muller(words[2], words[3]) if (q & 2) else oracle.box_muller(words[0], words[1])
+            g = pair[1] if (q & 1) else pair[0]
             want = np.float32(max(np.float32(0), clean[w, i] + sigma * g))
             assert abs(float(noisy[w, i]) - float(want)) <= 2e-6 * (1 + abs(float(want))), (w, i)
 

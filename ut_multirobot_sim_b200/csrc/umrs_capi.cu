@@ -2,8 +2,12 @@
 // device memory; there is no CPU fallback anywhere in this file: without a
 // usable device every compute entry point returns an error status.
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
+
+#include <algorithm>
 
 #include <atomic>
 #include <new>
@@ -75,8 +79,9 @@ namespace umrs {
 // shared with umrs_world.cu
 int capi_cuda_fail(cudaError_t e, const char* what) { return cuda_fail(e, what); }
 void capi_set_error(const char* msg) { g_last_cuda_error = msg; }
-struct MapView { const float4* d_segs; int32_t n; int smem_optin; };
-MapView capi_map_view(const umrs_map* m);
+struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; };
+int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
+                   int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
 }  // namespace umrs
 
 // ================================== map ==========================================
@@ -88,12 +93,85 @@ struct umrs_map {
   float4* d_segs = nullptr;
   cudaStream_t stream = nullptr;
   int32_t force_kernel = -1;
+  // uniform grid (K2): segments re-ordered by the cell of their midpoint
+  float4* d_sorted = nullptr;
+  int32_t* d_orig = nullptr;
+  int32_t* d_cell_start = nullptr;
+  int32_t gx = 0, gy = 0, n_binned = 0;
+  float gx0 = 0.f, gy0 = 0.f, cell = 1.f, inv_cell = 1.f, hmax_x = 0.f, hmax_y = 0.f;
   // scratch for the host-buffer scan entry points
   float4* d_fans = nullptr; size_t fans_cap = 0;
   float4* d_obj = nullptr;  size_t obj_cap = 0;
   float* d_ranges = nullptr; size_t ranges_cap = 0;
   int32_t* d_idx = nullptr;  size_t idx_cap = 0;
 };
+
+// Host-side, one-time (like VectorMap::Load/Cleanup): bin every segment by the
+// grid cell of its midpoint; segments longer than two cells go to an
+// always-visited tail.  Cell size: ~8 segments per cell on average.
+static cudaError_t build_grid(umrs_map* m) {
+  const int32_t n = m->n;
+  const float* s = m->host_segs.data();
+  float x0 = 0.f, y0 = 0.f, x1 = 1.f, y1 = 1.f;
+  for (int32_t i = 0; i < n; ++i) {
+    const float* q = s + 4 * i;
+    const float lx = std::min(q[0], q[2]), hx = std::max(q[0], q[2]);
+    const float ly = std::min(q[1], q[3]), hy = std::max(q[1], q[3]);
+    if (i == 0) { x0 = lx; x1 = hx; y0 = ly; y1 = hy; }
+    x0 = std::min(x0, lx); x1 = std::max(x1, hx);
+    y0 = std::min(y0, ly); y1 = std::max(y1, hy);
+  }
+  const float w = std::max(x1 - x0, 1e-3f), h = std::max(y1 - y0, 1e-3f);
+  float cell = sqrtf(8.0f * w * h / (float)std::max(n, 1));
+  cell = std::max(cell, std::max(w, h) / 2048.0f);
+  cell = std::max(cell, 1e-3f);
+  x0 -= 1e-3f * cell + 1e-5f * fabsf(x0);
+  y0 -= 1e-3f * cell + 1e-5f * fabsf(y0);
+  const float inv_cell = 1.0f / cell;
+  const int gx = std::max(1, (int)((x1 - x0) * inv_cell) + 1);
+  const int gy = std::max(1, (int)((y1 - y0) * inv_cell) + 1);
+  std::vector<int32_t> cell_of(n), count((size_t)gx * gy + 1, 0);
+  float hmx = 0.f, hmy = 0.f;
+  int32_t n_over = 0;
+  for (int32_t i = 0; i < n; ++i) {
+    const float* q = s + 4 * i;
+    const float mx = 0.5f * (q[0] + q[2]), my = 0.5f * (q[1] + q[3]);
+    const float hx = std::max(fabsf(q[0] - mx), fabsf(q[2] - mx));
+    const float hy = std::max(fabsf(q[1] - my), fabsf(q[3] - my));
+    if (!(hx <= cell && hy <= cell)) {  // also catches non-finite coordinates
+      cell_of[i] = -1;
+      ++n_over;
+      continue;
+    }
+    hmx = std::max(hmx, hx);
+    hmy = std::max(hmy, hy);
+    int cx = (int)((mx - x0) * inv_cell), cy = (int)((my - y0) * inv_cell);
+    cx = std::min(std::max(cx, 0), gx - 1);
+    cy = std::min(std::max(cy, 0), gy - 1);
+    cell_of[i] = cy * gx + cx;
+    ++count[(size_t)cell_of[i] + 1];
+  }
+  for (size_t c = 0; c < (size_t)gx * gy; ++c) count[c + 1] += count[c];
+  const int32_t n_binned = n - n_over;
+  std::vector<int32_t> cursor(count.begin(), count.end() - 1), orig(std::max(n, 1));
+  std::vector<float> sorted((size_t)std::max(n, 1) * 4);
+  int32_t tail = n_binned;
+  for (int32_t i = 0; i < n; ++i) {  // index order inside a cell
+    const int32_t k = cell_of[i] >= 0 ? cursor[cell_of[i]]++ : tail++;
+    orig[k] = i;
+    memcpy(&sorted[(size_t)k * 4], s + 4 * i, sizeof(float) * 4);
+  }
+  m->gx = gx; m->gy = gy; m->n_binned = n_binned;
+  m->gx0 = x0; m->gy0 = y0; m->cell = cell; m->inv_cell = inv_cell;
+  m->hmax_x = hmx * 1.0001f + 1e-6f; m->hmax_y = hmy * 1.0001f + 1e-6f;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&m->d_sorted), sizeof(float4) * (size_t)std::max(n, 1));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&m->d_orig), sizeof(int32_t) * (size_t)std::max(n, 1));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&m->d_cell_start), sizeof(int32_t) * count.size());
+  if (e == cudaSuccess && n > 0) e = cudaMemcpy(m->d_sorted, sorted.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && n > 0) e = cudaMemcpy(m->d_orig, orig.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(m->d_cell_start, count.data(), sizeof(int32_t) * count.size(), cudaMemcpyHostToDevice);
+  return e;
+}
 
 static int map_from_clean(const float* segs, int32_t n, umrs_map** out) {
   int dev = 0, smem = 0;
@@ -109,6 +187,7 @@ static int map_from_clean(const float* segs, int32_t n, umrs_map** out) {
   if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&m->d_segs), sizeof(float4) * (size_t)(n > 0 ? n : 1));
   if (e == cudaSuccess && n > 0)
     e = cudaMemcpy(m->d_segs, segs, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = build_grid(m);
   if (e != cudaSuccess) {
     int rc = cuda_fail(e, "umrs_map_create");
     umrs_map_destroy(m);
@@ -119,7 +198,53 @@ static int map_from_clean(const float* segs, int32_t n, umrs_map** out) {
 }
 
 namespace umrs {
-MapView capi_map_view(const umrs_map* m) { return MapView{m->d_segs, m->n, m->smem_optin}; }
+// Picks the kernel variant and the shared-memory plan for a launch against map m.
+//   K1 (kernel 0): every fan streams the whole map;  K2 (kernel 1): grid rows.
+// auto: K2 from 4096 map segments up.  cap = candidate slots per pass.
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
+                   int32_t n_obj_smem, int32_t n_ent, ScanPlan* out) {
+  ScanPlan pl;
+  memset(&pl, 0, sizeof(pl));
+  const bool grid = m->force_kernel == 1 || (m->force_kernel < 0 && m->n >= env_int("UMRS_GRID_FROM", 4096));
+  pl.kernel = grid ? 1 : 0;
+  pl.smem_optin = m->smem_optin;
+  MapSource& s = pl.src;
+  s.n = m->n;
+  s.n_map_total = m->n;
+  if (grid) {
+    s.segs = m->d_sorted; s.orig = m->d_orig; s.n_binned = m->n_binned;
+    s.cell_start = m->d_cell_start; s.gx = m->gx; s.gy = m->gy;
+    s.x0 = m->gx0; s.y0 = m->gy0; s.cell = m->cell; s.inv_cell = m->inv_cell;
+    s.hmax_x = m->hmax_x; s.hmax_y = m->hmax_y;
+    const double reach = 2.0 * ((double)range_max * 1.00002 + (double)m->hmax_y + 2e-3 * m->cell) ;
+    double rows = floor(reach * (double)m->inv_cell) + 3.0;
+    if (!(rows < (double)m->gy + 1.0)) rows = (double)m->gy + 1.0;  // also NaN / inf range_max
+    pl.max_rows = (int32_t)rows + 3;  // + long-segment tail + object row + spare
+  } else {
+    s.segs = m->d_segs; s.orig = nullptr; s.n_binned = m->n;
+    s.cell_start = nullptr; s.gx = 0; s.gy = 0;
+    pl.max_rows = 3;
+  }
+  const int cap_max = std::max(32, std::min(env_int("UMRS_CAP", 1024), 16384));
+  int64_t need = (int64_t)m->n + n_obj;
+  int32_t cap = (int32_t)std::min<int64_t>(std::max<int64_t>(need, 32), cap_max);
+  cap = (cap + 31) & ~31;
+  // shrink the per-pass slots until the CTA fits the opt-in shared memory
+  while (cap > 32 && scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent) > (size_t)m->smem_optin)
+    cap = ((cap / 2) + 31) & ~31;
+  if (scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent) > (size_t)m->smem_optin) {
+    capi_set_error("fan does not fit shared memory (too many rays / object lines per world)");
+    return UMRS_ERR_UNSUPPORTED;
+  }
+  pl.cap = cap;
+  *out = pl;
+  return UMRS_OK;
+}
 }  // namespace umrs
 
 extern "C" {
@@ -168,6 +293,9 @@ int umrs_map_load_file(const char* path, umrs_map** out) {
 int umrs_map_destroy(umrs_map* m) {
   if (m == NULL) return UMRS_OK;
   if (m->d_segs) cudaFree(m->d_segs);
+  if (m->d_sorted) cudaFree(m->d_sorted);
+  if (m->d_orig) cudaFree(m->d_orig);
+  if (m->d_cell_start) cudaFree(m->d_cell_start);
   if (m->d_fans) cudaFree(m->d_fans);
   if (m->d_obj) cudaFree(m->d_obj);
   if (m->d_ranges) cudaFree(m->d_ranges);
@@ -203,15 +331,19 @@ int umrs_scan_batch_device(umrs_map* m, const float* obj_segs_dev, int32_t n_obj
   if (m == NULL || n_fans < 0 || num_rays <= 0 || n_obj < 0 || ranges_dev == NULL ||
       (n_fans > 0 && fans_dev == NULL) || (n_obj > 0 && obj_segs_dev == NULL))
     return UMRS_ERR_INVALID;
-  const size_t smem = k1_smem_bytes(m->n + n_obj, 0, 0);
-  if (smem > (size_t)m->smem_optin || m->force_kernel == 1) {
-    g_last_cuda_error = "candidate set does not fit shared memory and the grid kernel is not built yet";
+  if (num_rays > kMaxRays) {
+    g_last_cuda_error = "num_rays above the per-fan limit";
     return UMRS_ERR_UNSUPPORTED;
   }
+  ScanPlan pl;
+  const int st = capi_scan_plan(m, range_max, n_obj, num_rays, 0, 0, &pl);
+  if (st != UMRS_OK) return st;
   ScanBatchParams p;
   memset(&p, 0, sizeof(p));
-  p.c.map_segs = m->d_segs;
-  p.c.n_map = m->n;
+  p.c.src = pl.src;
+  p.c.cap = pl.cap;
+  p.c.max_rows = pl.max_rows;
+  p.c.max_rays = num_rays;
   p.c.ranges = ranges_dev;
   p.c.hit_idx = hit_idx_dev;
   p.c.counters = nullptr;

@@ -6,6 +6,9 @@
 // round-to-nearest operation, exactly like the reference built with
 // -ffp-contract=off.  The places where the reference's expression promotes to
 // double (atan2, cos/sin in vector_map.cpp, AngleMod's rint) use double here too.
+// Where a cheaper evaluation is used it is explicit (__fmaf_rn, __fdividef,
+// atan2f) and comes with the argument for why every DECISION the reference
+// takes is unchanged.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -18,6 +21,7 @@ namespace umrs {
 constexpr double kPiD = 3.14159265358979323846;
 constexpr double k2PiD = 2.0 * kPiD;                 // M_2PI, math_util.h:28-30
 constexpr float k2PiF = 6.28318530717958647692f;     // T(M_2PI) for T = float
+constexpr float kPiF = 3.14159265358979323846f;
 
 // math_util::AngleMod<float>, math_util.h:55-59 (rint is the double C function
 // in vector_map.cpp's translation unit; the product and subtraction promote).
@@ -36,6 +40,58 @@ __device__ __forceinline__ float ray_angle(float angle_min, float da, int i) {
   return angle_mod_f(angle_min + (float)i * da);
 }
 
+// ---- per-fan ray lattice ----------------------------------------------------------
+// da = span / num_rays (vector_map.cpp:465).  cull_ok: the fan is a proper one
+// (positive step, at most one turn) so that a candidate's angular interval maps
+// to a ray-index interval; otherwise every candidate is tested against every ray
+// (still exact).  lazy_ok: endpoint angles may be taken from atan2f unless a ray
+// lies within `th_idx` index units of them (see make_cast).
+struct Lattice {
+  float amin, da, inv_da;
+  float period;      // rays per full turn
+  int p_lo, p_hi;    // integer bracket of period, for the wrapped image of a span
+  int num_rays;
+  bool cull_ok, lazy_ok;
+  float th_idx;
+};
+
+// Angular slack (rad) inside which an approximate endpoint angle could order
+// differently against a ray angle than the reference's float(atan2(double)):
+//   atan2f error <= 2 ulp + final rounding of the reference value 0.5 ulp,
+//   ulp(pi) = 2.4e-7                                           -> 6.0e-7
+//   ray angle vs its ideal lattice point (rounding of i*da, of the sum with
+//   angle_min, of AngleMod)                                    -> 8.4e-7
+//   float evaluation of (a - amin) mod 2pi and of u * inv_da at index <= 4096
+//                                                              -> 2.2e-6
+// sum 3.6e-6; 6e-6 is used.
+constexpr float kAngleSlack = 6e-6f;
+
+__device__ __forceinline__ Lattice make_lattice(float amin, float amax, int num_rays) {
+  Lattice L;
+  const float span = amax - amin;
+  L.amin = amin;
+  L.num_rays = num_rays;
+  L.da = span / (float)num_rays;
+  L.cull_ok = (L.da > 1e-7f) && (span <= 6.2832f);
+  L.inv_da = L.cull_ok ? 1.0f / L.da : 0.f;
+  L.period = L.cull_ok ? k2PiF * L.inv_da : 0.f;
+  L.p_hi = (int)ceilf(L.period) + 1;
+  L.p_lo = (int)floorf(L.period) - 1;
+  L.th_idx = kAngleSlack * L.inv_da;
+  L.lazy_ok = L.cull_ok && fabsf(amin) <= 8.0f && L.th_idx < 0.25f && num_rays <= 4096;
+  return L;
+}
+
+// True when some ray of the lattice may lie within kAngleSlack of angle a.
+__device__ __forceinline__ bool near_a_ray(const Lattice& L, float a) {
+  float u = a - L.amin;
+  u -= k2PiF * floorf(u * (1.0f / k2PiF));   // ~[0, 2pi]
+  const float t = u * L.inv_da;
+  const float d = fabsf(t - rintf(t));
+  // ray 0 also sits at u == 2pi, i.e. t == period (not an integer in general)
+  return d <= L.th_idx || fabsf(t - L.period) <= L.th_idx;
+}
+
 // Per-candidate constants of the ray fill (vector_map.cpp:444-459,471,473).
 // wraps_around is not stored: after the reference's swap, a wrapping interval
 // has a0 > a1 and a plain one a0 < a1 (|a0-a1| >= 1e-4 is guaranteed), so
@@ -47,14 +103,31 @@ struct SegCast {
   float arc;             // CCW extent a0 -> a1 in [0, pi], for chunk culling only
 };
 
-__device__ __forceinline__ SegCast make_cast(float4 s, float lx, float ly) {
+// Input: the segment already translated by -loc (vector_map.cpp:447-448).
+//
+// Lazily exact angles.  The reference computes a0/a1 as float(atan2(double))
+// (:449-450) and uses them ONLY in comparisons: |a0-a1| < 1e-4 (:451),
+// |a1-a0| > pi (:452), a0 < a1 (:453) and a0 <= a <= a1 against ray angles
+// (:469-470).  atan2f is within 6e-7 rad of that value; if neither threshold
+// comparison nor any ray comparison can come out differently (no ray within
+// kAngleSlack of either endpoint angle, both differences further than 4e-6
+// from their thresholds) the cheap angles are stored -- every decision, hence
+// every output bit, is the same.  Otherwise the double atan2 is evaluated.
+// The range itself never depends on a0/a1 beyond the swap decision.
+__device__ __forceinline__ SegCast make_cast(float p0x, float p0y, float p1x, float p1y,
+                                             const Lattice& L) {
   SegCast k;
   k.valid = false;
   k.a0 = 0.f; k.a1 = 0.f; k.nx = 0.f; k.ny = 0.f; k.c = 0.f; k.arc = 0.f;
-  float p0x = s.x - lx, p0y = s.y - ly;   // :447-448
-  float p1x = s.z - lx, p1y = s.w - ly;
-  float a0 = (float)atan2((double)p0y, (double)p0x);  // :449-450 (double atan2)
-  float a1 = (float)atan2((double)p1y, (double)p1x);
+  float a0 = atan2f(p0y, p0x);
+  float a1 = atan2f(p1y, p1x);
+  const float dab = fabsf(a0 - a1);
+  bool exact = !L.lazy_ok || fabsf(dab - 1e-4f) <= 4e-6f || fabsf(dab - kPiF) <= 4e-6f;
+  if (!exact) exact = near_a_ray(L, a0) || near_a_ray(L, a1);
+  if (exact) {
+    a0 = (float)atan2((double)p0y, (double)p0x);  // :449-450 (double atan2)
+    a1 = (float)atan2((double)p1y, (double)p1x);
+  }
   if (fabs((double)(a0 - a1)) < 0.0001) return k;     // :451
   const bool wraps = fabs((double)(a1 - a0)) > kPiD;  // :452
   if ((wraps && a0 < a1) || (!wraps && a0 > a1)) {    // :453-457
@@ -112,13 +185,16 @@ __device__ __forceinline__ uint4 philox4x32(uint4 c, uint2 k) {
   return c;
 }
 
-// Box-Muller on two words -> two N(0,1).
+// Box-Muller on two words -> two N(0,1).  The angle is 2*pi*y - pi in (-pi, pi)
+// (same distribution as 2*pi*y; keeps the fast sincos in its accurate range).
+// The noise is checked distributionally, not bitwise, so the hardware
+// log/sin/cos approximations are used (absolute error ~4e-7 each).
 __device__ __forceinline__ float2 box_muller(uint32_t u0, uint32_t u1) {
   const float x = ((float)(u0 >> 8) + 0.5f) * (1.0f / 16777216.0f);
   const float y = ((float)(u1 >> 8) + 0.5f) * (1.0f / 16777216.0f);
-  const float r = sqrtf(-2.0f * logf(x));
+  const float r = sqrtf(-2.0f * __logf(x));
   float s, c;
-  sincosf(k2PiF * y, &s, &c);
+  __sincosf(k2PiF * y - kPiF, &s, &c);
   return make_float2(r * c, r * s);
 }
 

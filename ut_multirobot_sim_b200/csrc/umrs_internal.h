@@ -37,15 +37,37 @@ struct HumanState {
 static_assert(sizeof(HumanState) == 64, "HumanState must be 64 B");
 
 constexpr int kAgeNever = 1 << 28;
-constexpr int kScanThreads = 128;  // 4 warps per fan CTA
+constexpr int kScanThreads = 256;  // 8 warps per fan CTA
+constexpr int kMaxRays = 16384;    // per fan (bounded by the per-ray best arrays in smem)
 
-// ---- K1 parameters -------------------------------------------------------------
+// ---- where a fan's candidate segments come from ----------------------------------
+// K1 ("shared-memory scan"): gx == 0, the whole cleaned map [0, n) in index order.
+// K2 ("uniform-grid walk"):  the map re-ordered by the grid cell of each segment's
+// midpoint (row-major cells), so that the cells [cx0, cx1] of one grid row are ONE
+// contiguous range of `segs`; segments longer than two cells are kept in an
+// always-visited tail [n_binned, n).  orig[k] = index of sorted segment k in the
+// caller's map (the hit index the reference's GetSceneLines order defines,
+// vector_map.cpp:200-214).
+struct MapSource {
+  const float4* segs;
+  const int32_t* orig;        // nullptr: identity
+  int32_t n;
+  int32_t n_binned;           // == n when gx == 0
+  const int32_t* cell_start;  // [gx * gy + 1], into segs
+  int32_t gx, gy;
+  float x0, y0, cell, inv_cell;
+  float hmax_x, hmax_y;       // max |endpoint - midpoint| over binned segments
+  int32_t n_map_total;        // object line o gets hit index n_map_total + o
+};
+
 struct ScanCommon {
-  const float4* map_segs;  // cleaned map, {x0,y0,x1,y1} per segment
-  int32_t n_map;
-  float* ranges;           // [fans][num_rays] or [W][rays_per_world]
-  int32_t* hit_idx;        // nullable, same shape
-  unsigned long long* counters;  // nullable: {tests, segs_prepared, chunk_seg_pairs}
+  MapSource src;
+  float* ranges;                 // [fans][num_rays] or [W][rays_per_world]
+  int32_t* hit_idx;              // nullable, same shape
+  unsigned long long* counters;  // nullable: {tests, segs_prepared, chunk_seg_pairs, passes}
+  int32_t cap;                   // candidate slots per pass (smem sizing)
+  int32_t max_rows;              // source rows a fan can touch (smem sizing)
+  int32_t max_rays;              // largest num_rays of any fan of the launch (smem sizing)
 };
 
 struct ScanBatchParams {
@@ -61,6 +83,8 @@ struct ScanBatchParams {
 struct WorldStepParams {
   ScanCommon c;
   int32_t W, R, H, O;
+  int32_t world_first;              // first world of this launch (slices of one step)
+  int32_t world_count;
   const umrs_robot_params* robots;  // [R]
   const umrs_human_params* humans;  // [H]
   const float4* tmpl;               // [L_obj] template line of world-line l
@@ -87,15 +111,13 @@ struct WorldStepParams {
   int32_t laser_noise, motion_noise;
 };
 
-// Dynamic shared memory a K1 CTA needs for n_cand candidates (+ n_obj world
-// lines and n_ent entities when the step is fused).
-size_t k1_smem_bytes(int n_cand, int n_obj_lines, int n_ent);
+// Dynamic shared memory of one fan CTA.
+size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent);
 
 cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream);
 cudaError_t launch_world_step(const WorldStepParams& p, cudaStream_t stream);
 cudaError_t launch_stats(const float* ranges, size_t n, double* out4_dev,
                          cudaStream_t stream);
-cudaError_t k1_configure(size_t smem_bytes);
 
 // Launch accounting (umrs_kernel_launch_count).
 void note_launch(int n = 1);

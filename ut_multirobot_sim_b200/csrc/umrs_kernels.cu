@@ -1,6 +1,7 @@
-// K1: shared-memory scan kernel (+ fused world step), sm_100a.
+// Scan kernels (K1 shared-memory scan, K2 uniform-grid walk) and the fused world
+// step, sm_100a.  One CTA = one ray fan (one robot's LaserScan of one world).
 //
-// One CTA = one ray fan (one robot's LaserScan of one world).  Replaces
+// Replaces
 //   VectorMap::GetPredictedScan   vector_map.cpp:420-478   (per-ray fill)
 //   VectorMap::SceneRender        vector_map.cpp:217-258   (NOT reproduced: the
 //       O(L^2) occlusion trimming is replaced by a per-ray minimum over all
@@ -9,16 +10,26 @@
 // and, in the world-step form, Simulator::update + publishLaser
 //   (simulator.cpp:474-509, 393-426) with the model Step()s.
 //
-// Phases of a CTA:
+// Phases of a CTA (scan_fan):
 //   A  (world step only) integrate every entity of the world, build the
 //      world's object lines in shared memory
-//   B  candidate pre-pass, one thread per candidate segment: AABB cull,
-//      translate, two double atan2, unit normal -> {a0,a1,nx,ny | c | ray-index
-//      span} records in shared memory
-//   C  ray loop: a warp owns 32 consecutive rays (lane = ray); lanes first act
-//      as 32 parallel cull testers over the span table (ballot), then every
-//      surviving candidate is broadcast from shared memory and tested by all
-//      32 rays with the reference's inclusive angular predicate
+//   then, per PASS over at most `cap` source segments (one pass unless the
+//   fan's source set is larger than the shared-memory slots):
+//   S1 gather: threads stream the fan's source rows (the whole map for K1; the
+//      grid rows overlapping [loc +- range_max] for K2; then the object lines),
+//      apply the reference's AABB cull and compact the survivors' translated
+//      end points + hit index into shared memory (warp ballot + one atomic)
+//   S2 records: one thread per survivor: lazily exact end-point angles, swap,
+//      unit normal -> {a0,a1,nx,ny | c}; conservative ray-index span; the span
+//      is turned into per-32-ray-chunk BUCKETS (count, scan, fill) so that the
+//      ray loop only ever touches candidates that can cover its rays
+//   C  ray loop: a warp owns 32 consecutive rays (lane = ray), chunks handed out
+//      dynamically; every bucket entry is broadcast from shared memory and
+//      tested by the 32 rays with the reference's inclusive angular predicate;
+//      the running winner is selected on a 2-ulp quotient, the winner's range
+//      is then evaluated with the reference's exact expression
+//   F  finalise: publishLaser post-process (dropout + Philox noise), coalesced
+//      stores of ranges / hit indices
 #include "umrs_device.cuh"
 #include "umrs_internal.h"
 
@@ -26,33 +37,83 @@ namespace umrs {
 
 // ---- shared-memory carve-up --------------------------------------------------
 struct SmemView {
-  float4* rec4;   // [n_cand] {a0, a1, nx, ny}
-  float* recc;    // [n_cand] c
-  int2* span;     // [n_cand] conservative ray-index interval {lo, hi}; lo > hi = dead
-  float4* obj;    // [n_obj_lines] world object lines (world step only)
-  float* ent;     // [n_ent][5] {x, y, theta, sin, cos} (world step only)
+  float4* rec4;      // [cap] S1: translated {p0x,p0y,p1x,p1y}; S2: {a0, a1, nx, ny}
+  float* recc;       // [cap] c = n . p0'
+  int32_t* idx;      // [cap] hit index of the slot (GetSceneLines order)
+  int2* span;        // [cap] conservative ray-index interval {lo, hi}; lo > hi = dead
+  uint16_t* pool;    // [3*cap] bucket entries (slots), grouped by chunk
+  uint16_t* wide;    // [cap] slots that did not fit the pool: span-checked per chunk
+  float* best_r;     // [max_rays] range of the running winner (the reference's exact expression)
+  float* best_q;     // [max_rays] the 2-ulp quotient the winner was selected on (pass to pass)
+  int32_t* best_i;   // [max_rays] its hit index (-1: none)
+  int32_t* cnt;      // [n_chunks_max] bucket sizes (cursor while filling)
+  int32_t* start;    // [n_chunks_max] bucket offsets into pool
+  int32_t* row_v0;   // [max_rows + 1] first virtual index of source row r
+  int32_t* row_s0;   // [max_rows] first source index of row r (object row: 0)
+  int32_t* ctl;      // [8] n_cand, pool_used, n_wide, next_chunk, n_rows, ...
+  float4* obj;       // [n_obj_lines] world object lines (world step only)
+  float* ent;        // [n_ent][5] {x, y, theta, sin, cos} (world step only)
 };
+enum { kCtlNCand = 0, kCtlPoolUsed = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
-size_t k1_smem_bytes(int n_cand, int n_obj_lines, int n_ent) {
-  size_t b = 0;
-  b += align16(sizeof(float4) * (size_t)n_cand);
-  b += align16(sizeof(float) * (size_t)n_cand);
-  b += align16(sizeof(int2) * (size_t)n_cand);
-  b += align16(sizeof(float4) * (size_t)n_obj_lines);
-  b += align16(sizeof(float) * 5 * (size_t)n_ent);
-  return b;
+struct SmemOffsets { size_t o[17]; };
+
+__host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int max_rays,
+                                                   int n_obj_lines, int n_ent) {
+  const size_t n_chunks = (size_t)((max_rays + 31) >> 5);
+  const size_t sizes[16] = {
+      sizeof(float4) * (size_t)cap,            // rec4
+      sizeof(float) * (size_t)cap,             // recc
+      sizeof(int32_t) * (size_t)cap,           // idx
+      sizeof(int2) * (size_t)cap,              // span
+      sizeof(uint16_t) * 3 * (size_t)cap,      // pool
+      sizeof(uint16_t) * (size_t)cap,          // wide
+      sizeof(float) * (size_t)max_rays,        // best_r
+      sizeof(int32_t) * (size_t)max_rays,      // best_i
+      sizeof(int32_t) * n_chunks,              // cnt
+      sizeof(int32_t) * n_chunks,              // start
+      sizeof(int32_t) * (size_t)(max_rows + 1),  // row_v0
+      sizeof(int32_t) * (size_t)(max_rows + 1),  // row_s0
+      sizeof(int32_t) * 8,                     // ctl
+      sizeof(float4) * (size_t)n_obj_lines,    // obj
+      sizeof(float) * 5 * (size_t)n_ent,       // ent
+      sizeof(float) * (size_t)max_rays};       // best_q
+  SmemOffsets L;
+  size_t o = 0;
+  for (int k = 0; k < 16; ++k) {
+    L.o[k] = o;
+    o += align16(sizes[k]);
+  }
+  L.o[16] = o;
+  return L;
 }
 
-__device__ inline SmemView carve(unsigned char* base, int n_cand, int n_obj_lines) {
+size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent) {
+  return smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent).o[16];
+}
+
+__device__ inline SmemView carve(unsigned char* base, int cap, int max_rows, int max_rays,
+                                 int n_obj_lines, int n_ent) {
+  const SmemOffsets L = smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent);
   SmemView v;
-  size_t o = 0;
-  v.rec4 = reinterpret_cast<float4*>(base + o); o += align16(sizeof(float4) * (size_t)n_cand);
-  v.recc = reinterpret_cast<float*>(base + o);  o += align16(sizeof(float) * (size_t)n_cand);
-  v.span = reinterpret_cast<int2*>(base + o);   o += align16(sizeof(int2) * (size_t)n_cand);
-  v.obj = reinterpret_cast<float4*>(base + o);  o += align16(sizeof(float4) * (size_t)n_obj_lines);
-  v.ent = reinterpret_cast<float*>(base + o);
+  v.rec4 = reinterpret_cast<float4*>(base + L.o[0]);
+  v.recc = reinterpret_cast<float*>(base + L.o[1]);
+  v.idx = reinterpret_cast<int32_t*>(base + L.o[2]);
+  v.span = reinterpret_cast<int2*>(base + L.o[3]);
+  v.pool = reinterpret_cast<uint16_t*>(base + L.o[4]);
+  v.wide = reinterpret_cast<uint16_t*>(base + L.o[5]);
+  v.best_r = reinterpret_cast<float*>(base + L.o[6]);
+  v.best_i = reinterpret_cast<int32_t*>(base + L.o[7]);
+  v.cnt = reinterpret_cast<int32_t*>(base + L.o[8]);
+  v.start = reinterpret_cast<int32_t*>(base + L.o[9]);
+  v.row_v0 = reinterpret_cast<int32_t*>(base + L.o[10]);
+  v.row_s0 = reinterpret_cast<int32_t*>(base + L.o[11]);
+  v.ctl = reinterpret_cast<int32_t*>(base + L.o[12]);
+  v.obj = reinterpret_cast<float4*>(base + L.o[13]);
+  v.ent = reinterpret_cast<float*>(base + L.o[14]);
+  v.best_q = reinterpret_cast<float*>(base + L.o[15]);
   return v;
 }
 
@@ -63,172 +124,367 @@ struct Fan {
   float range_max;
 };
 
-// ---- phase B: candidate pre-pass ----------------------------------------------
-// Candidate j < n_map is map segment j; j >= n_map is object line j - n_map
-// (GetSceneLines order).  Object lines [skip_lo, skip_hi) are the fan's own body.
-__device__ void prepass(const SmemView& sm, const Fan& fan, const float4* __restrict__ map_segs,
-                        int n_map, const float4* obj_segs, int n_obj, int skip_lo,
-                        int skip_hi, unsigned long long* counters) {
-  const float da = (fan.amax - fan.amin) / (float)fan.num_rays;  // vector_map.cpp:465
-  // Conservative ray-index estimate; the exact decision is the float predicate
-  // in the ray loop.  If the fan is degenerate or wider than one turn every
-  // candidate spans all rays (plain brute force, still exact).
-  const bool cull_ok = (da > 1e-7f) && ((fan.amax - fan.amin) <= 6.2832f);
-  const float inv_da = cull_ok ? 1.0f / da : 0.f;
-  int n_valid = 0;
-  for (int j = threadIdx.x; j < n_map + n_obj; j += blockDim.x) {
-    float4 s;
-    bool keep = true;
-    if (j < n_map) {
-      s = __ldg(map_segs + j);
-    } else {
-      const int o = j - n_map;
-      s = obj_segs[o];
-      keep = !(o >= skip_lo && o < skip_hi);
-    }
-    keep = keep && aabb_keep(s, fan.lx, fan.ly, fan.range_max);
-    SegCast k;
-    k.valid = false;
-    if (keep) k = make_cast(s, fan.lx, fan.ly);
-    int2 sp = make_int2(1, 0);
-    if (k.valid) {
-      ++n_valid;
-      if (cull_ok) {
-        float u0 = k.a0 - fan.amin;
-        u0 -= k2PiF * floorf(u0 / k2PiF);              // [0, 2pi)
-        sp.x = (int)floorf(u0 * inv_da) - 2;
-        sp.y = (int)ceilf((u0 + k.arc) * inv_da) + 2;
-      } else {
-        sp = make_int2(0, 0x3fffffff);
-      }
-    }
-    sm.rec4[j] = make_float4(k.a0, k.a1, k.nx, k.ny);
-    sm.recc[j] = k.c;
-    sm.span[j] = sp;
-  }
-  if (counters != nullptr) {
-    // one atomic per warp
-    for (int o = 16; o > 0; o >>= 1) n_valid += __shfl_down_sync(0xffffffffu, n_valid, o);
-    if ((threadIdx.x & 31) == 0 && n_valid) atomicAdd(counters + 1, (unsigned long long)n_valid);
-  }
-}
-
-// ---- phase C: ray loop ----------------------------------------------------------
-// Returns nothing; writes ranges/idx for the whole fan.  When `post` is set the
-// publishLaser post-process (simulator.cpp:412-418) is applied with Philox noise.
+// publishLaser post-process (simulator.cpp:412-418) with Philox noise.
 struct PostProcess {
   bool enabled;
   float stddev;
   uint32_t key0, key1, step_lo, step_hi, fan_global;
 };
 
-__device__ void ray_loop(const SmemView& sm, const Fan& fan, int n_cand, float* __restrict__ ranges,
-                         int32_t* __restrict__ hit_idx, const PostProcess& post,
+// ---- source rows of a fan -----------------------------------------------------------
+// Virtual index space = concatenation of the rows; row r covers virtual
+// [row_v0[r], row_v0[r+1]) = source [row_s0[r], ...).  The LAST row is always the
+// object-line row (possibly empty).  Written by thread 0.
+__device__ void build_rows(const SmemView& sm, const MapSource& src, const Fan& fan, int n_obj,
+                           int max_rows) {
+  int r = 0, v = 0;
+  if (src.gx == 0) {
+    sm.row_v0[r] = v; sm.row_s0[r] = 0; v += src.n; ++r;
+  } else {
+    // cells whose binned segments (by midpoint) can pass the AABB cull: widen the
+    // query box by the largest midpoint-to-endpoint offset, plus a margin that
+    // dominates every float rounding in this computation and in the host binning
+    const float mx = src.hmax_x + 1e-3f * src.cell + 1e-5f * (fabsf(fan.lx) + fan.range_max);
+    const float my = src.hmax_y + 1e-3f * src.cell + 1e-5f * (fabsf(fan.ly) + fan.range_max);
+    const float fx0 = ((fan.lx - fan.range_max - mx) - src.x0) * src.inv_cell;
+    const float fx1 = ((fan.lx + fan.range_max + mx) - src.x0) * src.inv_cell;
+    const float fy0 = ((fan.ly - fan.range_max - my) - src.y0) * src.inv_cell;
+    const float fy1 = ((fan.ly + fan.range_max + my) - src.y0) * src.inv_cell;
+    // NaN-safe clamps (a NaN pose yields an empty set)
+    int cx0 = fx0 > 0.f ? (fx0 < (float)src.gx ? (int)fx0 : src.gx) : 0;
+    int cx1 = fx1 >= 0.f ? (fx1 < (float)src.gx ? (int)fx1 : src.gx - 1) : -1;
+    int cy0 = fy0 > 0.f ? (fy0 < (float)src.gy ? (int)fy0 : src.gy) : 0;
+    int cy1 = fy1 >= 0.f ? (fy1 < (float)src.gy ? (int)fy1 : src.gy - 1) : -1;
+    if (!(fx0 == fx0) || !(fx1 == fx1) || !(fy0 == fy0) || !(fy1 == fy1)) cx1 = -1;
+    if (cx0 <= cx1) {
+      for (int cy = cy0; cy <= cy1 && r < max_rows - 2; ++cy) {
+        const int s0 = __ldg(src.cell_start + cy * src.gx + cx0);
+        const int s1 = __ldg(src.cell_start + cy * src.gx + cx1 + 1);
+        if (s1 > s0) { sm.row_v0[r] = v; sm.row_s0[r] = s0; v += s1 - s0; ++r; }
+      }
+    }
+    // always-visited tail: segments longer than two cells
+    if (src.n > src.n_binned) {
+      sm.row_v0[r] = v; sm.row_s0[r] = src.n_binned; v += src.n - src.n_binned; ++r;
+    }
+  }
+  sm.row_v0[r] = v; sm.row_s0[r] = 0; v += n_obj; ++r;   // object row
+  sm.row_v0[r] = v;
+  sm.ctl[kCtlNRows] = r;
+}
+
+// ---- S1: gather + AABB cull + compaction ------------------------------------------
+// Virtual indices [v_begin, v_end) of this pass.  Object lines [skip_lo, skip_hi)
+// are the fan's own body.
+__device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
+                       const float4* obj_segs, int skip_lo, int skip_hi, int v_begin, int v_end) {
+  const int n_rows = sm.ctl[kCtlNRows];
+  const int lane = threadIdx.x & 31;
+  // iterate in warp-uniform trip counts so that the ballots are full-warp
+  for (int vb = v_begin + (int)(threadIdx.x & ~31u); vb < v_end; vb += blockDim.x) {
+    const int v = vb + lane;
+    bool keep = false;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    int hit = -1;
+    if (v < v_end) {
+      // row of v: the table is short (2 rows for K1, a few dozen for K2)
+      int lo = 0, hi = n_rows - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (sm.row_v0[mid] <= v) lo = mid; else hi = mid - 1;
+      }
+      const int k = v - sm.row_v0[lo];
+      if (lo == n_rows - 1) {
+        s = obj_segs[k];
+        hit = src.n_map_total + k;
+        keep = !(k >= skip_lo && k < skip_hi);
+      } else {
+        const int si = sm.row_s0[lo] + k;
+        s = __ldg(src.segs + si);
+        hit = src.orig ? __ldg(src.orig + si) : si;
+        keep = true;
+      }
+      keep = keep && aabb_keep(s, fan.lx, fan.ly, fan.range_max);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    int base = 0;
+    if (lane == 0 && m) base = atomicAdd(&sm.ctl[kCtlNCand], __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (keep) {
+      const int pos = base + __popc(m & ((1u << lane) - 1u));
+      // translate by -loc (vector_map.cpp:447-448)
+      sm.rec4[pos] = make_float4(s.x - fan.lx, s.y - fan.ly, s.z - fan.lx, s.w - fan.ly);
+      sm.idx[pos] = hit;
+    }
+  }
+}
+
+// ---- span -> chunk ranges ------------------------------------------------------------
+constexpr int kWideFlag = 0x40000000;
+
+struct ChunkRanges {
+  int xa, xb;   // chunks of the span itself        (empty: xa > xb)
+  int ya, yb;   // chunks of its image one turn down (empty: ya > yb)
+};
+
+__device__ __forceinline__ ChunkRanges chunk_ranges(int lo, int hi, const Lattice& L) {
+  ChunkRanges c;
+  const int last = L.num_rays - 1;
+  int l1 = lo < 0 ? 0 : lo, h1 = hi > last ? last : hi;
+  c.xa = l1 >> 5; c.xb = h1 >> 5;
+  if (l1 > h1) { c.xa = 1; c.xb = 0; }
+  int l2 = lo - L.p_hi, h2 = hi - L.p_lo;
+  l2 = l2 < 0 ? 0 : l2; h2 = h2 > last ? last : h2;
+  c.ya = l2 >> 5; c.yb = h2 >> 5;
+  if (l2 > h2 || !L.cull_ok) { c.ya = 1; c.yb = 0; }
+  if (c.xa <= c.xb && c.ya <= c.yb && c.yb >= c.xa) {   // overlapping images: one range
+    c.xa = c.ya < c.xa ? c.ya : c.xa;
+    c.xb = c.yb > c.xb ? c.yb : c.xb;
+    c.ya = 1; c.yb = 0;
+  }
+  return c;
+}
+
+// ---- S2: records, spans, bucket counts -----------------------------------------------
+__device__ void make_records(const SmemView& sm, const Lattice& L, int cap,
+                             unsigned long long* counters) {
+  const int n_cand = sm.ctl[kCtlNCand];
+  int n_valid = 0;
+  for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
+    const float4 p = sm.rec4[slot];
+    const SegCast k = make_cast(p.x, p.y, p.z, p.w, L);
+    int2 sp = make_int2(1, 0);
+    if (k.valid) {
+      ++n_valid;
+      if (L.cull_ok) {
+        // Conservative ray-index estimate; the exact decision is the float
+        // predicate in the ray loop.
+        float u0 = k.a0 - L.amin;
+        u0 -= k2PiF * floorf(u0 / k2PiF);              // [0, 2pi)
+        sp.x = (int)floorf(u0 * L.inv_da) - 2;
+        sp.y = (int)ceilf((u0 + k.arc) * L.inv_da) + 2;
+      } else {
+        sp = make_int2(0, L.num_rays - 1);
+      }
+      const ChunkRanges cr = chunk_ranges(sp.x, sp.y, L);
+      const int n = (cr.xa <= cr.xb ? cr.xb - cr.xa + 1 : 0) + (cr.ya <= cr.yb ? cr.yb - cr.ya + 1 : 0);
+      if (n == 0) {
+        sp = make_int2(1, 0);                          // outside the fan
+      } else {
+        const int pos = atomicAdd(&sm.ctl[kCtlPoolUsed], n);
+        if (pos + n <= 3 * cap) {
+          for (int c = cr.xa; c <= cr.xb; ++c) atomicAdd(&sm.cnt[c], 1);
+          for (int c = cr.ya; c <= cr.yb; ++c) atomicAdd(&sm.cnt[c], 1);
+        } else {
+          sm.wide[atomicAdd(&sm.ctl[kCtlNWide], 1)] = (uint16_t)slot;
+          sp.y |= kWideFlag;
+        }
+      }
+    }
+    sm.rec4[slot] = make_float4(k.a0, k.a1, k.nx, k.ny);
+    sm.recc[slot] = k.c;
+    sm.span[slot] = sp;
+  }
+  if (counters != nullptr) {
+    for (int o = 16; o > 0; o >>= 1) n_valid += __shfl_down_sync(0xffffffffu, n_valid, o);
+    if ((threadIdx.x & 31) == 0 && n_valid) atomicAdd(counters + 1, (unsigned long long)n_valid);
+  }
+}
+
+// cnt[] -> start[] (exclusive scan), cnt[] reset to serve as the fill cursor.  Warp 0.
+__device__ void scan_buckets(const SmemView& sm, int n_chunks) {
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  int run = 0;
+  for (int base = 0; base < n_chunks; base += 32) {
+    const int c = base + lane;
+    const int v = c < n_chunks ? sm.cnt[c] : 0;
+    int x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (c < n_chunks) { sm.start[c] = run + x - v; sm.cnt[c] = 0; }
+    run += __shfl_sync(0xffffffffu, x, 31);
+  }
+}
+
+__device__ void fill_buckets(const SmemView& sm, const Lattice& L) {
+  const int n_cand = sm.ctl[kCtlNCand];
+  for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
+    const int2 sp = sm.span[slot];
+    if (sp.x > sp.y || (sp.y & kWideFlag)) continue;
+    const ChunkRanges cr = chunk_ranges(sp.x, sp.y, L);
+    for (int c = cr.xa; c <= cr.xb; ++c) sm.pool[sm.start[c] + atomicAdd(&sm.cnt[c], 1)] = (uint16_t)slot;
+    for (int c = cr.ya; c <= cr.yb; ++c) sm.pool[sm.start[c] + atomicAdd(&sm.cnt[c], 1)] = (uint16_t)slot;
+  }
+}
+
+// ---- C: ray loop ----------------------------------------------------------------------
+__device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, int pass,
                          unsigned long long* counters) {
   const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int n_warps = blockDim.x >> 5;
-  const float span_f = fan.amax - fan.amin;
-  const float da = span_f / (float)fan.num_rays;
-  const bool cull_ok = (da > 1e-7f) && (span_f <= 6.2832f);
-  // rays per full turn, bracketed for the wrapped image of a candidate's span
-  const float period = cull_ok ? k2PiF / da : 0.f;
-  const int p_hi = (int)ceilf(period) + 1, p_lo = (int)floorf(period) - 1;
   const int n_chunks = (fan.num_rays + 31) >> 5;
-  unsigned long long n_tests = 0, n_pairs = 0;
+  const int n_wide = sm.ctl[kCtlNWide];
+  unsigned long long n_pairs = 0;
+  const float inf = __int_as_float(0x7f800000);
 
-  for (int chunk = warp; chunk < n_chunks; chunk += n_warps) {
+  for (;;) {
+    int chunk = 0;
+    if (lane == 0) chunk = atomicAdd(&sm.ctl[kCtlNextChunk], 1);
+    chunk = __shfl_sync(0xffffffffu, chunk, 0);
+    if (chunk >= n_chunks) break;
     const int i = (chunk << 5) + lane;
     const bool live = i < fan.num_rays;
     const int cs = chunk << 5, ce = cs + 31;
     float a = __int_as_float(0x7fc00000);  // NaN: covers nothing
     float rx = 0.f, ry = 0.f;
     if (live) {
-      a = ray_angle(fan.amin, da, i);                    // vector_map.cpp:467
+      a = ray_angle(L.amin, L.da, i);                    // vector_map.cpp:467
       double sd, cd;
       sincos((double)a, &sd, &cd);                       // :472 double cos/sin
       rx = (float)cd;
       ry = (float)sd;
     }
-    float best = __int_as_float(0x7f800000);  // +inf
-    int best_j = -1;
-    for (int base = 0; base < n_cand; base += 32) {
-      const int j = base + lane;
-      bool ov = false;
-      if (j < n_cand) {
-        const int2 sp = sm.span[j];
-        ov = (sp.x <= ce && sp.y >= cs) || (sp.x - p_hi <= ce && sp.y - p_lo >= cs);
-        ov = ov && (sp.x <= sp.y);
-      }
-      unsigned m = __ballot_sync(0xffffffffu, ov);
-      n_pairs += __popc(m);
-      while (m) {
-        const int b = __ffs(m) - 1;
-        m &= m - 1;
-        const int jj = base + b;
-        const float4 r4 = sm.rec4[jj];                   // broadcast LDS.128
-        if (cast_covers(r4.x, r4.y, a)) {                // :469-470
-          const float den = r4.z * rx + r4.w * ry;       // n.dot(r)
-          const float r = sm.recc[jj] / den;             // :473
-          if (r < best) {                                // first strictly smaller wins
-            best = r;
-            best_j = jj;
-          }
+    float best = (pass > 0 && live) ? sm.best_q[i] : inf;
+    const int prev_i = (pass > 0 && live) ? sm.best_i[i] : -1;
+    if (prev_i < 0) best = inf;
+    int best_slot = -1;
+
+    // One candidate against the 32 rays of the chunk.  The winner is selected on
+    // q = c / (n . r) evaluated with one FMA and the 2-ulp hardware quotient; the
+    // reference's exact expression is evaluated once, for the winner, below.
+    // Equal q: lowest hit index wins (the reference's scan order with a strict <).
+    auto test = [&](int slot) {
+      const float4 r4 = sm.rec4[slot];                   // broadcast LDS.128
+      if (cast_covers(r4.x, r4.y, a)) {                  // :469-470
+        const float den = __fmaf_rn(r4.z, rx, r4.w * ry);
+        const float q = __fdividef(sm.recc[slot], den);
+        if (q < best) {
+          best = q;
+          best_slot = slot;
+        } else if (q == best) {
+          const int other = best_slot >= 0 ? sm.idx[best_slot] : prev_i;
+          if (sm.idx[slot] < other) best_slot = slot;
         }
       }
+    };
+
+    for (int e = 0; e < n_wide; ++e) {
+      const int slot = sm.wide[e];
+      const int2 sp = sm.span[slot];
+      const int hi = sp.y & ~kWideFlag;
+      if ((sp.x <= ce && hi >= cs) || (L.cull_ok && sp.x - L.p_hi <= ce && hi - L.p_lo >= cs)) {
+        test(slot);
+        ++n_pairs;
+      }
     }
-    if (counters != nullptr) n_tests += (unsigned long long)0;  // filled below
+    const int nb = sm.cnt[chunk];
+    const uint16_t* bucket = sm.pool + sm.start[chunk];
+    for (int e = 0; e < nb; ++e) test(bucket[e]);
+    n_pairs += nb;
+
     if (live) {
-      float out = best_j >= 0 ? best : fan.range_max;    // :433 fill value
+      if (best_slot >= 0) {
+        const float4 r4 = sm.rec4[best_slot];
+        const float den = r4.z * rx + r4.w * ry;         // n.dot(r), vector_map.cpp:473
+        sm.best_r[i] = sm.recc[best_slot] / den;
+        sm.best_q[i] = best;
+        sm.best_i[i] = sm.idx[best_slot];
+      } else if (pass == 0) {
+        sm.best_r[i] = inf;
+        sm.best_i[i] = -1;
+      }
+    }
+  }
+  if (counters != nullptr && lane == 0 && n_pairs) {
+    atomicAdd(counters + 2, n_pairs);
+    atomicAdd(counters + 0, n_pairs * 32ull);  // tests = pairs x 32 lanes
+  }
+}
+
+// ---- F: finalise ------------------------------------------------------------------------
+// Noise counter layout: ray i = 128*s + 32*q + l (l < 32, q < 4) takes normal q of
+// Philox block {32*s + l, fan_global, step_lo, step_hi ^ 'LASR'} -- one Philox call
+// and two Box-Muller transforms serve four rays, and a warp's stores stay coalesced.
+__device__ void finalise(const SmemView& sm, const Fan& fan, float* __restrict__ ranges,
+                         int32_t* __restrict__ hit_idx, const PostProcess& post) {
+  const int n_blocks = ((fan.num_rays + 127) >> 7) << 5;
+  for (int b = threadIdx.x; b < n_blocks; b += blockDim.x) {
+    float g[4] = {0.f, 0.f, 0.f, 0.f};
+    if (post.enabled) {
+      const uint4 w = philox4x32(make_uint4((uint32_t)b, post.fan_global, post.step_lo,
+                                            post.step_hi ^ kStreamLaser),
+                                 make_uint2(post.key0, post.key1));
+      const float2 g01 = box_muller(w.x, w.y), g23 = box_muller(w.z, w.w);
+      g[0] = g01.x; g[1] = g01.y; g[2] = g23.x; g[3] = g23.y;
+    }
+    const int i0 = ((b >> 5) << 7) + (b & 31);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int i = i0 + (q << 5);
+      if (i >= fan.num_rays) break;
+      const int bi = sm.best_i[i];
+      float out = bi >= 0 ? sm.best_r[i] : fan.range_max;   // :433 fill value
       if (post.enabled) {
         // simulator.cpp:412-418; range_max - 0.1 is a double expression
-        if ((double)out > (double)fan.range_max - 0.1) {
-          out = 0.f;
-        } else {
-          const uint4 w = philox4x32(
-              make_uint4((uint32_t)(i >> 2), post.fan_global, post.step_lo,
-                         post.step_hi ^ kStreamLaser),
-              make_uint2(post.key0, post.key1));
-          const float2 g = (i & 2) ? box_muller(w.z, w.w) : box_muller(w.x, w.y);
-          const float gi = (i & 1) ? g.y : g.x;
-          out = fmaxf(0.f, out + post.stddev * gi);
-        }
+        if ((double)out > (double)fan.range_max - 0.1) out = 0.f;
+        else out = fmaxf(0.f, out + post.stddev * g[q]);
       }
       ranges[i] = out;
-      if (hit_idx != nullptr) hit_idx[i] = best_j;
+      if (hit_idx != nullptr) hit_idx[i] = bi;
     }
   }
-  if (counters != nullptr) {
-    // chunk-candidate pairs are warp-uniform; tests = pairs * 32 lanes
-    if (lane == 0 && n_pairs) {
-      atomicAdd(counters + 2, n_pairs);
-      atomicAdd(counters + 0, n_pairs * 32ull);
-    }
-    (void)n_tests;
+}
+
+// ---- one fan, all passes --------------------------------------------------------------
+__device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan,
+                         const float4* obj_segs, int n_obj, int skip_lo, int skip_hi,
+                         float* ranges, int32_t* hit_idx, const PostProcess& post) {
+  const Lattice L = make_lattice(fan.amin, fan.amax, fan.num_rays);
+  const int n_chunks = (fan.num_rays + 31) >> 5;
+  if (threadIdx.x == 0) build_rows(sm, c.src, fan, n_obj, c.max_rows);
+  __syncthreads();
+  const int v_total = sm.row_v0[sm.ctl[kCtlNRows]];
+  int pass = 0;
+  for (int v0 = 0; v0 < v_total || pass == 0; v0 += c.cap, ++pass) {
+    if (threadIdx.x < 4) sm.ctl[threadIdx.x] = 0;   // n_cand, pool_used, n_wide, next_chunk
+    for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) sm.cnt[k] = 0;
+    __syncthreads();
+    const int v1 = v0 + c.cap < v_total ? v0 + c.cap : v_total;
+    gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1);
+    __syncthreads();
+    make_records(sm, L, c.cap, c.counters);
+    __syncthreads();
+    scan_buckets(sm, n_chunks);
+    __syncthreads();
+    fill_buckets(sm, L);
+    __syncthreads();
+    ray_loop(sm, fan, L, pass, c.counters);
+    __syncthreads();
   }
+  if (c.counters != nullptr && threadIdx.x == 0) atomicAdd(c.counters + 3, (unsigned long long)pass);
+  finalise(sm, fan, ranges, hit_idx, post);
 }
 
 // ---- scan-only kernel (umrs_predicted_scan / umrs_scan_batch) -------------------
 __global__ void __launch_bounds__(kScanThreads)
-k1_scan_batch(const __grid_constant__ ScanBatchParams p) {
+k_scan_batch(const __grid_constant__ ScanBatchParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int n_cand = p.c.n_map + p.n_obj;
-  const SmemView sm = carve(smem_raw, n_cand, 0);
+  const SmemView sm = carve(smem_raw, p.c.cap, p.c.max_rows, p.c.max_rays, 0, 0);
   for (int f = blockIdx.x; f < p.n_fans; f += gridDim.x) {
     const float4 fp = __ldg(p.fans + f);
     Fan fan;
     fan.lx = fp.x; fan.ly = fp.y; fan.amin = fp.z; fan.amax = fp.w;
     fan.num_rays = p.num_rays;
     fan.range_max = p.range_max;
-    __syncthreads();  // previous fan's ray loop is done with the records
-    prepass(sm, fan, p.c.map_segs, p.c.n_map, p.obj_segs, p.n_obj, 0, 0, p.c.counters);
-    __syncthreads();
     PostProcess post;
     post.enabled = false;
     post.stddev = 0.f; post.key0 = post.key1 = post.step_lo = post.step_hi = post.fan_global = 0;
     const size_t off = (size_t)f * (size_t)p.num_rays;
-    ray_loop(sm, fan, n_cand, p.c.ranges + off,
-             p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, p.c.counters);
+    __syncthreads();  // previous fan's finalise is done with the best arrays
+    scan_fan(sm, p.c, fan, p.obj_segs, p.n_obj, 0, 0, p.c.ranges + off,
+             p.c.hit_idx ? p.c.hit_idx + off : nullptr, post);
   }
 }
 
@@ -391,20 +647,19 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
 }
 
 // ---- fused world-step kernel -------------------------------------------------
-// grid = W * R fans; CTA (w, r).  Every CTA of world w integrates ALL entities of
-// that world (R + H tiny steps, redundantly across the R CTAs) from the
-// read-only "in" state so that no inter-CTA exchange is needed; the r == 0 CTA
-// alone writes the "out" state (ping-pong buffers).  Order as in
+// grid = world_count * R fans; CTA (w, r).  Every CTA of world w integrates ALL
+// entities of that world (R + H tiny steps, redundantly across the R CTAs) from
+// the read-only "in" state so that no inter-CTA exchange is needed; the r == 0
+// CTA alone writes the "out" state (ping-pong buffers).  Order as in
 // Simulator::Run (simulator.cpp:531-541): update() first, scan from the
 // post-step pose against the post-step object lines.
 __global__ void __launch_bounds__(kScanThreads)
-k1_world_step(const __grid_constant__ WorldStepParams p) {
+k_world_step(const __grid_constant__ WorldStepParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int n_cand = p.c.n_map + p.L_obj;
   const int n_ent = p.O + p.H + p.R;
-  const SmemView sm = carve(smem_raw, n_cand, p.L_obj);
-  const int w = blockIdx.x / p.R;
-  const int r = blockIdx.x - w * p.R;
+  const SmemView sm = carve(smem_raw, p.c.cap, p.c.max_rows, p.c.max_rays, p.L_obj, n_ent);
+  const int w = p.world_first + (int)(blockIdx.x / (unsigned)p.R);
+  const int r = (int)(blockIdx.x % (unsigned)p.R);
   const bool owner = (r == 0);
   const double dt = (double)p.dt;  // `const double& dt` bound to float CONFIG_DT
   const int t = threadIdx.x;
@@ -489,13 +744,10 @@ k1_world_step(const __grid_constant__ WorldStepParams p) {
     fan.range_max = me.laser.range_max;
   }
   if (t == 0 && p.fan_params != nullptr)
-    p.fan_params[blockIdx.x] = make_float4(fan.lx, fan.ly, fan.amin, fan.amax);
+    p.fan_params[(size_t)w * p.R + r] = make_float4(fan.lx, fan.ly, fan.amin, fan.amax);
   __syncthreads();
 
   const int skip_lo = p.ent_off[p.O + p.H + r], skip_hi = p.ent_off[p.O + p.H + r + 1];
-  prepass(sm, fan, p.c.map_segs, p.c.n_map, sm.obj, p.L_obj, skip_lo, skip_hi, p.c.counters);
-  __syncthreads();
-
   PostProcess post;
   post.enabled = p.laser_noise != 0;
   post.stddev = me.laser.noise_stddev;
@@ -503,12 +755,12 @@ k1_world_step(const __grid_constant__ WorldStepParams p) {
   post.step_lo = p.step_lo; post.step_hi = p.step_hi;
   post.fan_global = (uint32_t)(p.world_base + w) * (uint32_t)p.R + (uint32_t)r;
   const size_t off = (size_t)w * (size_t)p.rays_per_world + (size_t)p.ray_off[r];
-  ray_loop(sm, fan, n_cand, p.c.ranges + off,
-           p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, p.c.counters);
+  scan_fan(sm, p.c, fan, sm.obj, p.L_obj, skip_lo, skip_hi, p.c.ranges + off,
+           p.c.hit_idx ? p.c.hit_idx + off : nullptr, post);
 }
 
 // ---- K3: statistics of a ranges buffer -------------------------------------------
-// out4 = {count of finite positive ranges, min, max, sum}; one atomic set per CTA.
+// out4 = {count of finite positive ranges, min, max, sum}; one atomic set per warp.
 __global__ void k3_stats(const float* __restrict__ ranges, size_t n, double* out4) {
   double cnt = 0.0, sum = 0.0;
   float mn = __int_as_float(0x7f800000), mx = 0.f;
@@ -538,37 +790,41 @@ __global__ void k3_stats(const float* __restrict__ ranges, size_t n, double* out
 }
 
 // ---- launchers ----------------------------------------------------------------
-static size_t g_k1_smem_configured = 0;
+static size_t g_smem_configured_dev[64];
 
-cudaError_t k1_configure(size_t smem_bytes) {
-  if (smem_bytes <= g_k1_smem_configured) return cudaSuccess;
-  cudaError_t e = cudaFuncSetAttribute(k1_scan_batch, cudaFuncAttributeMaxDynamicSharedMemorySize,
+static cudaError_t configure_smem(size_t smem_bytes) {
+  int dev = 0;
+  cudaError_t e0 = cudaGetDevice(&dev);
+  if (e0 != cudaSuccess) return e0;
+  size_t& g_smem_configured = g_smem_configured_dev[dev & 63];
+  if (smem_bytes <= g_smem_configured) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(k_scan_batch, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k1_world_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  e = cudaFuncSetAttribute(k_world_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  g_k1_smem_configured = smem_bytes;
+  g_smem_configured = smem_bytes;
   return cudaSuccess;
 }
 
 cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream) {
   if (p.n_fans <= 0) return cudaSuccess;
-  const size_t smem = k1_smem_bytes(p.c.n_map + p.n_obj, 0, 0);
-  cudaError_t e = k1_configure(smem);
+  const size_t smem = scan_smem_bytes(p.c.cap, p.c.max_rows, p.c.max_rays, 0, 0);
+  cudaError_t e = configure_smem(smem);
   if (e != cudaSuccess) return e;
-  k1_scan_batch<<<p.n_fans, kScanThreads, smem, stream>>>(p);
+  k_scan_batch<<<p.n_fans, kScanThreads, smem, stream>>>(p);
   note_launch();
   return cudaGetLastError();
 }
 
 cudaError_t launch_world_step(const WorldStepParams& p, cudaStream_t stream) {
-  const int fans = p.W * p.R;
+  const int fans = p.world_count * p.R;
   if (fans <= 0) return cudaSuccess;
-  const size_t smem = k1_smem_bytes(p.c.n_map + p.L_obj, p.L_obj, p.O + p.H + p.R);
-  cudaError_t e = k1_configure(smem);
+  const size_t smem = scan_smem_bytes(p.c.cap, p.c.max_rows, p.c.max_rays, p.L_obj, p.O + p.H + p.R);
+  cudaError_t e = configure_smem(smem);
   if (e != cudaSuccess) return e;
-  k1_world_step<<<fans, kScanThreads, smem, stream>>>(p);
+  k_world_step<<<fans, kScanThreads, smem, stream>>>(p);
   note_launch();
   return cudaGetLastError();
 }

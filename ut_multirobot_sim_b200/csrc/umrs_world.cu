@@ -19,8 +19,9 @@ struct umrs_map;
 namespace umrs {
 int capi_cuda_fail(cudaError_t e, const char* what);
 void capi_set_error(const char* msg);
-struct MapView { const float4* d_segs; int32_t n; int smem_optin; };
-MapView capi_map_view(const umrs_map* m);
+struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; };
+int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
+                   int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
 }  // namespace umrs
 
 #define UMRS_CUDA(call)                                          \
@@ -33,7 +34,8 @@ struct umrs_world {
   umrs_world_desc desc;
   std::vector<umrs_robot_params> robots;
   std::vector<umrs_human_params> humans;
-  MapView map;
+  ScanPlan plan;  // kernel variant + shared-memory plan, fixed at creation
+  int32_t max_rays = 0;
   int32_t W = 0, R = 0, H = 0, O = 0;
   int32_t L_obj = 0, rays_per_world = 0;
   std::vector<int32_t> ent_off, ray_off, num_rays;
@@ -99,7 +101,6 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (w->H > 0) w->humans.assign(d->humans, d->humans + w->H);
   w->desc.robots = nullptr;
   w->desc.humans = nullptr;
-  w->map = capi_map_view(map);
 
   // ---- object-line roster: [statics][humans][robot bodies] ---------------------
   std::vector<float> tmpl;      // xyxy per world-line
@@ -149,11 +150,23 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   }
   w->rays_per_world = w->ray_off.back();
 
-  const size_t smem = k1_smem_bytes(w->map.n + w->L_obj, w->L_obj, w->O + w->H + w->R);
-  if (smem > (size_t)w->map.smem_optin) {
-    capi_set_error("world candidate set does not fit shared memory");
+  float range_max = 0.f;
+  for (int r = 0; r < w->R; ++r) {
+    w->max_rays = w->num_rays[r] > w->max_rays ? w->num_rays[r] : w->max_rays;
+    range_max = w->robots[r].laser.range_max > range_max ? w->robots[r].laser.range_max : range_max;
+  }
+  if (w->max_rays > kMaxRays || w->L_obj > 16384) {
+    capi_set_error("too many rays per fan or object lines per world");
     umrs_world_destroy(w);
     return UMRS_ERR_UNSUPPORTED;
+  }
+  {
+    const int st = capi_scan_plan(map, range_max, w->L_obj, w->max_rays, w->L_obj,
+                                  w->O + w->H + w->R, &w->plan);
+    if (st != UMRS_OK) {
+      umrs_world_destroy(w);
+      return st;
+    }
   }
 
   // ---- device allocations -----------------------------------------------------------
@@ -325,12 +338,15 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
                         cudaStream_t stream) {
   WorldStepParams p;
   memset(&p, 0, sizeof(p));
-  p.c.map_segs = w->map.d_segs;
-  p.c.n_map = w->map.n;
+  p.c.src = w->plan.src;
+  p.c.cap = w->plan.cap;
+  p.c.max_rows = w->plan.max_rows;
+  p.c.max_rays = w->max_rays;
   p.c.ranges = w->d_ranges;
   p.c.hit_idx = w->d_idx;
   p.c.counters = w->counters_on ? w->d_counters : nullptr;
   p.W = w->W; p.R = w->R; p.H = w->H; p.O = w->O;
+  p.world_first = 0; p.world_count = w->W;
   p.robots = w->d_robots;
   p.humans = w->d_humans;
   p.tmpl = w->d_tmpl;
