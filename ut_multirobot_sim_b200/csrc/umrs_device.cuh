@@ -40,6 +40,38 @@ __device__ __forceinline__ float ray_angle(float angle_min, float da, int i) {
   return angle_mod_f(angle_min + (float)i * da);
 }
 
+// cos/sin of a ray angle as the reference evaluates them (vector_map.cpp:472:
+// the double functions on a float angle, narrowed to float).  |a| <= pi after
+// AngleMod, so the general-argument machinery of sincos() is not needed:
+// Cody-Waite reduction by k*pi/2 (two-part constant, exact for |k| <= 2) and the
+// fdlibm kernel polynomials on [-pi/4, pi/4] give both values to ~1 ulp in
+// double, i.e. the same float after rounding as any other faithful double
+// implementation (the GPU/glibc pair already in use agreed on every ray tested).
+__device__ __forceinline__ void ray_dir(float a, float& rx, float& ry) {
+  const float kf = rintf(a * 0.636619772367581343f);   // nearest multiple of pi/2
+  const double k = (double)kf;
+  double r = fma(-k, 1.57079632673412561417e+00, (double)a);
+  r = fma(-k, 6.07710050650619224932e-11, r);
+  const double z = r * r;
+  double ps = fma(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
+  ps = fma(z, ps, 2.75573137070700676789e-06);
+  ps = fma(z, ps, -1.98412698298579493134e-04);
+  ps = fma(z, ps, 8.33333333332248946124e-03);
+  ps = fma(z, ps, -1.66666666666666324348e-01);
+  const double sn = fma(z * r, ps, r);
+  double pc = fma(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
+  pc = fma(z, pc, -2.75573143513906633035e-07);
+  pc = fma(z, pc, 2.48015872894767294178e-05);
+  pc = fma(z, pc, -1.38888888888741095749e-03);
+  pc = fma(z, pc, 4.16666666666666019037e-02);
+  const double cs = 1.0 - fma(z, 0.5, -(z * z) * pc);
+  const int q = (int)kf & 3;
+  const double c = (q & 1) ? sn : cs, s = (q & 1) ? cs : sn;
+  // q: 0 (s, c)  1 (c, -s)  2 (-s, -c)  3 (-c, s)   [as (sin, cos)]
+  rx = (float)((q == 1 || q == 2) ? -c : c);
+  ry = (float)((q == 2 || q == 3) ? -s : s);
+}
+
 // ---- per-fan ray lattice ----------------------------------------------------------
 // da = span / num_rays (vector_map.cpp:465).  cull_ok: the fan is a proper one
 // (positive step, at most one turn) so that a candidate's angular interval maps

@@ -41,13 +41,13 @@ struct SmemView {
   float* recc;       // [cap] c = n . p0'
   int32_t* idx;      // [cap] hit index of the slot (GetSceneLines order)
   int2* span;        // [cap] conservative ray-index interval {lo, hi}; lo > hi = dead
-  uint16_t* pool;    // [3*cap] bucket entries (slots), grouped by chunk
-  uint16_t* wide;    // [cap] slots that did not fit the pool: span-checked per chunk
+  uint16_t* pool;    // [3*cap] bucket entries (slots): chunk c owns [c*K, (c+1)*K)
+  uint16_t* wide;    // [cap] slots that met a full bucket: span-checked per chunk
   float* best_r;     // [max_rays] range of the running winner (the reference's exact expression)
   float* best_q;     // [max_rays] the 2-ulp quotient the winner was selected on (pass to pass)
   int32_t* best_i;   // [max_rays] its hit index (-1: none)
-  int32_t* cnt;      // [n_chunks_max] bucket sizes (cursor while filling)
-  int32_t* start;    // [n_chunks_max] bucket offsets into pool
+  int32_t* cnt;      // [n_chunks_max] (wrapping entries << 16) | plain entries of the bucket
+  int32_t* start;    // [n_chunks_max] (spare)
   int32_t* row_v0;   // [max_rows + 1] first virtual index of source row r
   int32_t* row_s0;   // [max_rows] first source index of row r (object row: 0)
   int32_t* ctl;      // [8] n_cand, pool_used, n_wide, next_chunk, n_rows, ...
@@ -68,7 +68,7 @@ __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int ma
       sizeof(float) * (size_t)cap,             // recc
       sizeof(int32_t) * (size_t)cap,           // idx
       sizeof(int2) * (size_t)cap,              // span
-      sizeof(uint16_t) * 3 * (size_t)cap,      // pool
+      sizeof(uint16_t) * (3 * (size_t)cap > 8 * n_chunks ? 3 * (size_t)cap : 8 * n_chunks),  // pool
       sizeof(uint16_t) * (size_t)cap,          // wide
       sizeof(float) * (size_t)max_rays,        // best_r
       sizeof(int32_t) * (size_t)max_rays,      // best_i
@@ -220,8 +220,6 @@ __device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
 }
 
 // ---- span -> chunk ranges ------------------------------------------------------------
-constexpr int kWideFlag = 0x40000000;
-
 struct ChunkRanges {
   int xa, xb;   // chunks of the span itself        (empty: xa > xb)
   int ya, yb;   // chunks of its image one turn down (empty: ya > yb)
@@ -245,8 +243,19 @@ __device__ __forceinline__ ChunkRanges chunk_ranges(int lo, int hi, const Lattic
   return c;
 }
 
-// ---- S2: records, spans, bucket counts -----------------------------------------------
-__device__ void make_records(const SmemView& sm, const Lattice& L, int cap,
+// Bucket of chunk c = pool[c*K, (c+1)*K): plain intervals (a0 < a1) fill it from
+// the front, wrapping ones (a0 > a1) from the back, so that the ray loop tests
+// each kind with a two-compare predicate.  cnt[c] = (n_wrap << 16) | n_plain.
+// A candidate that meets a full bucket goes to the `wide` list instead, which
+// the ray loop span-checks per chunk (it may then be tested twice in chunks that
+// had room -- harmless for a minimum).
+__device__ __forceinline__ int bucket_capacity(int cap, int n_chunks) {
+  int k = ((3 * cap) / n_chunks) & ~7;
+  return k < 8 ? 8 : (k > 248 ? 248 : k);
+}
+
+// ---- S2: records, spans, buckets ------------------------------------------------------
+__device__ void make_records(const SmemView& sm, const Lattice& L, int K,
                              unsigned long long* counters) {
   const int n_cand = sm.ctl[kCtlNCand];
   int n_valid = 0;
@@ -267,18 +276,26 @@ __device__ void make_records(const SmemView& sm, const Lattice& L, int cap,
         sp = make_int2(0, L.num_rays - 1);
       }
       const ChunkRanges cr = chunk_ranges(sp.x, sp.y, L);
-      const int n = (cr.xa <= cr.xb ? cr.xb - cr.xa + 1 : 0) + (cr.ya <= cr.yb ? cr.yb - cr.ya + 1 : 0);
-      if (n == 0) {
+      if (cr.xa > cr.xb && cr.ya > cr.yb) {
         sp = make_int2(1, 0);                          // outside the fan
       } else {
-        const int pos = atomicAdd(&sm.ctl[kCtlPoolUsed], n);
-        if (pos + n <= 3 * cap) {
-          for (int c = cr.xa; c <= cr.xb; ++c) atomicAdd(&sm.cnt[c], 1);
-          for (int c = cr.ya; c <= cr.yb; ++c) atomicAdd(&sm.cnt[c], 1);
-        } else {
-          sm.wide[atomicAdd(&sm.ctl[kCtlNWide], 1)] = (uint16_t)slot;
-          sp.y |= kWideFlag;
+        const bool wrap = k.a0 > k.a1;
+        const int inc = wrap ? 0x10000 : 1;
+        bool spilled = false;
+        for (int part = 0; part < 2; ++part) {
+          const int ca = part ? cr.ya : cr.xa, cb = part ? cr.yb : cr.xb;
+          for (int c = ca; c <= cb; ++c) {
+            const int old = atomicAdd(&sm.cnt[c], inc);
+            const int na = old & 0xffff, nb = old >> 16;
+            if (na + nb < K) {
+              sm.pool[c * K + (wrap ? K - 1 - nb : na)] = (uint16_t)slot;
+            } else {
+              atomicSub(&sm.cnt[c], inc);   // bucket full: stays full from here on
+              spilled = true;
+            }
+          }
         }
+        if (spilled) sm.wide[atomicAdd(&sm.ctl[kCtlNWide], 1)] = (uint16_t)slot;
       }
     }
     sm.rec4[slot] = make_float4(k.a0, k.a1, k.nx, k.ny);
@@ -291,37 +308,8 @@ __device__ void make_records(const SmemView& sm, const Lattice& L, int cap,
   }
 }
 
-// cnt[] -> start[] (exclusive scan), cnt[] reset to serve as the fill cursor.  Warp 0.
-__device__ void scan_buckets(const SmemView& sm, int n_chunks) {
-  if (threadIdx.x >= 32) return;
-  const int lane = threadIdx.x;
-  int run = 0;
-  for (int base = 0; base < n_chunks; base += 32) {
-    const int c = base + lane;
-    const int v = c < n_chunks ? sm.cnt[c] : 0;
-    int x = v;
-    for (int o = 1; o < 32; o <<= 1) {
-      const int y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (c < n_chunks) { sm.start[c] = run + x - v; sm.cnt[c] = 0; }
-    run += __shfl_sync(0xffffffffu, x, 31);
-  }
-}
-
-__device__ void fill_buckets(const SmemView& sm, const Lattice& L) {
-  const int n_cand = sm.ctl[kCtlNCand];
-  for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
-    const int2 sp = sm.span[slot];
-    if (sp.x > sp.y || (sp.y & kWideFlag)) continue;
-    const ChunkRanges cr = chunk_ranges(sp.x, sp.y, L);
-    for (int c = cr.xa; c <= cr.xb; ++c) sm.pool[sm.start[c] + atomicAdd(&sm.cnt[c], 1)] = (uint16_t)slot;
-    for (int c = cr.ya; c <= cr.yb; ++c) sm.pool[sm.start[c] + atomicAdd(&sm.cnt[c], 1)] = (uint16_t)slot;
-  }
-}
-
 // ---- C: ray loop ----------------------------------------------------------------------
-__device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, int pass,
+__device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, int K, int pass,
                          unsigned long long* counters) {
   const int lane = threadIdx.x & 31;
   const int n_chunks = (fan.num_rays + 31) >> 5;
@@ -341,48 +329,69 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
     float rx = 0.f, ry = 0.f;
     if (live) {
       a = ray_angle(L.amin, L.da, i);                    // vector_map.cpp:467
-      double sd, cd;
-      sincos((double)a, &sd, &cd);                       // :472 double cos/sin
-      rx = (float)cd;
-      ry = (float)sd;
+      ray_dir(a, rx, ry);                                // :472
     }
-    float best = (pass > 0 && live) ? sm.best_q[i] : inf;
     const int prev_i = (pass > 0 && live) ? sm.best_i[i] : -1;
-    if (prev_i < 0) best = inf;
+    const float prev_q = prev_i >= 0 ? sm.best_q[i] : inf;
+    float best = prev_q;
     int best_slot = -1;
+    bool tie = false;
 
     // One candidate against the 32 rays of the chunk.  The winner is selected on
     // q = c / (n . r) evaluated with one FMA and the 2-ulp hardware quotient; the
     // reference's exact expression is evaluated once, for the winner, below.
-    // Equal q: lowest hit index wins (the reference's scan order with a strict <).
-    auto test = [&](int slot) {
-      const float4 r4 = sm.rec4[slot];                   // broadcast LDS.128
-      if (cast_covers(r4.x, r4.y, a)) {                  // :469-470
-        const float den = __fmaf_rn(r4.z, rx, r4.w * ry);
-        const float q = __fdividef(sm.recc[slot], den);
-        if (q < best) {
-          best = q;
-          best_slot = slot;
-        } else if (q == best) {
-          const int other = best_slot >= 0 ? sm.idx[best_slot] : prev_i;
-          if (sm.idx[slot] < other) best_slot = slot;
-        }
-      }
-    };
+    // An equal q is only flagged here; see the careful sweep below.
+#define UMRS_TEST(SLOT, COVER_EXPR)                                              \
+    {                                                                            \
+      const int s_ = (SLOT);                                                     \
+      const float4 r4 = sm.rec4[s_];                  /* broadcast LDS.128 */    \
+      const float den = __fmaf_rn(r4.z, rx, r4.w * ry);                          \
+      const float q = __fdividef(sm.recc[s_], den);                              \
+      const bool cov = (COVER_EXPR);                  /* :469-470 */             \
+      tie = tie || (cov && q == best);                                           \
+      if (cov && q < best) { best = q; best_slot = s_; }                         \
+    }
 
+    const int packed = sm.cnt[chunk];
+    const int n_plain = packed & 0xffff, n_wrap = packed >> 16;
+    const uint16_t* bucket = sm.pool + chunk * K;
+    {
+      int e = 0;
+      for (; e + 1 < n_plain; e += 2) {               // two candidates in flight
+        const uint32_t two = *reinterpret_cast<const uint32_t*>(bucket + e);
+        UMRS_TEST((int)(two & 0xffffu), r4.x <= a && a <= r4.y)
+        UMRS_TEST((int)(two >> 16), r4.x <= a && a <= r4.y)
+      }
+      if (e < n_plain) UMRS_TEST((int)bucket[e], r4.x <= a && a <= r4.y)
+    }
+    for (int e = 0; e < n_wrap; ++e) UMRS_TEST((int)bucket[K - 1 - e], r4.x <= a || a <= r4.y)
+    n_pairs += n_plain + n_wrap;
     for (int e = 0; e < n_wide; ++e) {
       const int slot = sm.wide[e];
       const int2 sp = sm.span[slot];
-      const int hi = sp.y & ~kWideFlag;
-      if ((sp.x <= ce && hi >= cs) || (L.cull_ok && sp.x - L.p_hi <= ce && hi - L.p_lo >= cs)) {
-        test(slot);
+      if ((sp.x <= ce && sp.y >= cs) || (L.cull_ok && sp.x - L.p_hi <= ce && sp.y - L.p_lo >= cs)) {
+        UMRS_TEST(slot, cast_covers(r4.x, r4.y, a))
         ++n_pairs;
       }
     }
-    const int nb = sm.cnt[chunk];
-    const uint16_t* bucket = sm.pool + sm.start[chunk];
-    for (int e = 0; e < nb; ++e) test(bucket[e]);
-    n_pairs += nb;
+#undef UMRS_TEST
+
+    // Careful sweep, only if some ray of the chunk saw two candidates with the
+    // same q: lowest hit index wins (the reference's scan order with a strict <).
+    if (__any_sync(0xffffffffu, tie)) {
+      int best_idx = best_slot >= 0 ? sm.idx[best_slot] : prev_i;
+      auto careful = [&](int slot) {
+        const float4 r4 = sm.rec4[slot];
+        if (!cast_covers(r4.x, r4.y, a)) return;
+        const float den = __fmaf_rn(r4.z, rx, r4.w * ry);
+        const float q = __fdividef(sm.recc[slot], den);
+        const int id = sm.idx[slot];
+        if (q == best && id < best_idx) { best_slot = slot; best_idx = id; }
+      };
+      for (int e = 0; e < n_plain; ++e) careful(bucket[e]);
+      for (int e = 0; e < n_wrap; ++e) careful(bucket[K - 1 - e]);
+      for (int e = 0; e < n_wide; ++e) careful(sm.wide[e]);
+    }
 
     if (live) {
       if (best_slot >= 0) {
@@ -443,25 +452,26 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
                          float* ranges, int32_t* hit_idx, const PostProcess& post) {
   const Lattice L = make_lattice(fan.amin, fan.amax, fan.num_rays);
   const int n_chunks = (fan.num_rays + 31) >> 5;
+  const int K = bucket_capacity(c.cap, n_chunks);
   if (threadIdx.x == 0) build_rows(sm, c.src, fan, n_obj, c.max_rows);
+  if (threadIdx.x >= 32 && threadIdx.x < 36) sm.ctl[threadIdx.x - 32] = 0;
+  for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) sm.cnt[k] = 0;
   __syncthreads();
   const int v_total = sm.row_v0[sm.ctl[kCtlNRows]];
   int pass = 0;
   for (int v0 = 0; v0 < v_total || pass == 0; v0 += c.cap, ++pass) {
-    if (threadIdx.x < 4) sm.ctl[threadIdx.x] = 0;   // n_cand, pool_used, n_wide, next_chunk
-    for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) sm.cnt[k] = 0;
-    __syncthreads();
     const int v1 = v0 + c.cap < v_total ? v0 + c.cap : v_total;
     gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1);
     __syncthreads();
-    make_records(sm, L, c.cap, c.counters);
+    make_records(sm, L, K, c.counters);
     __syncthreads();
-    scan_buckets(sm, n_chunks);
+    ray_loop(sm, fan, L, K, pass, c.counters);
     __syncthreads();
-    fill_buckets(sm, L);
-    __syncthreads();
-    ray_loop(sm, fan, L, pass, c.counters);
-    __syncthreads();
+    if (v0 + c.cap < v_total) {   // another pass: reset the per-pass state
+      if (threadIdx.x < 4) sm.ctl[threadIdx.x] = 0;
+      for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) sm.cnt[k] = 0;
+      __syncthreads();
+    }
   }
   if (c.counters != nullptr && threadIdx.x == 0) atomicAdd(c.counters + 3, (unsigned long long)pass);
   finalise(sm, fan, ranges, hit_idx, post);
