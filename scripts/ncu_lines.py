@@ -42,3 +42,25 @@ ts = sum(v[2] for v in agg.values()) or 1
 print("sum over lines: inst %d samples %d (all profiled launches, nested inlines counted per level)" % (tot, ts))
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1])[:top]:
     print("%-20s %4d %6.2f%% inst %6.2f%% smp  %s" % (k[0], k[1], 100 * v[1] / tot, 100 * v[2] / ts, v[0][:90]))
+
+# ---- per-function shares (file, first line of each function found by a crude scan) ----
+import os, re, bisect
+root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "ut_multirobot_sim_b200", "csrc")
+funcs = {}
+for fn in ("umrs_kernels.cu", "umrs_device.cuh"):
+    starts = []
+    for n, line in enumerate(open(os.path.join(root, fn)), 1):
+        m = re.match(r"^(?:__device__|__global__|template|static|cudaError_t|size_t).*?(\w+)\s*\(", line)
+        if m and not line.startswith(" "):
+            starts.append((n, m.group(1)))
+    funcs[fn] = starts
+by = {}
+for (f, ln), v in agg.items():
+    name = f
+    if f in funcs and funcs[f]:
+        k = bisect.bisect_right([s[0] for s in funcs[f]], ln) - 1
+        name = f + ":" + (funcs[f][k][1] if k >= 0 else "?")
+    b = by.setdefault(name, [0, 0]); b[0] += v[1]; b[1] += v[2]
+print("---- per function ----")
+for k, v in sorted(by.items(), key=lambda kv: -kv[1][0])[:25]:
+    print("%-45s %6.2f%% inst %6.2f%% smp" % (k, 100 * v[0] / tot, 100 * v[1] / ts))

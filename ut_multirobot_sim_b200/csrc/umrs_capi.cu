@@ -230,7 +230,7 @@ int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t ma
     s.cell_start = nullptr; s.gx = 0; s.gy = 0;
     pl.max_rows = 3;
   }
-  const int cap_max = std::max(32, std::min(env_int("UMRS_CAP", 1024), 16384));
+  const int cap_max = std::max(32, std::min(env_int("UMRS_CAP", 1536), 16384));
   int64_t need = (int64_t)m->n + n_obj;
   int32_t cap = (int32_t)std::min<int64_t>(std::max<int64_t>(need, 32), cap_max);
   cap = (cap + 31) & ~31;

@@ -463,9 +463,11 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     const int v1 = v0 + c.cap < v_total ? v0 + c.cap : v_total;
     gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1);
     __syncthreads();
-    make_records(sm, L, K, c.counters);
-    __syncthreads();
-    ray_loop(sm, fan, L, K, pass, c.counters);
+    if (pass == 0 || sm.ctl[kCtlNCand] > 0) {   // block-uniform: a later pass may be empty
+      make_records(sm, L, K, c.counters);
+      __syncthreads();
+      ray_loop(sm, fan, L, K, pass, c.counters);
+    }
     __syncthreads();
     if (v0 + c.cap < v_total) {   // another pass: reset the per-pass state
       if (threadIdx.x < 4) sm.ctl[threadIdx.x] = 0;
