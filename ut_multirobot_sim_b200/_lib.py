@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libumrs.so")
+# UMRS_LIB: alternative build of the same library (kernel-variant A/B runs)
+LIB_PATH = os.environ.get("UMRS_LIB") or os.path.join(_HERE, "libumrs.so")
 
 UMRS_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_NO_DEVICE, ERR_IO = 1, 2, 3, 4, 5, 6

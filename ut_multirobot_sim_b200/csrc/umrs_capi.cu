@@ -79,7 +79,7 @@ namespace umrs {
 // shared with umrs_world.cu
 int capi_cuda_fail(cudaError_t e, const char* what) { return cuda_fail(e, what); }
 void capi_set_error(const char* msg) { g_last_cuda_error = msg; }
-struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; };
+struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; int32_t multipass; };
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
 }  // namespace umrs
@@ -230,14 +230,20 @@ int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t ma
     s.cell_start = nullptr; s.gx = 0; s.gy = 0;
     pl.max_rows = 3;
   }
-  const int cap_max = std::max(32, std::min(env_int("UMRS_CAP", 1536), 16384));
+  // bucket entries are 16 * slot in 16 bits -> at most 4064 slots per pass
+  const int cap_max = std::max(32, std::min(env_int("UMRS_CAP", 1536), 4064));
   int64_t need = (int64_t)m->n + n_obj;
   int32_t cap = (int32_t)std::min<int64_t>(std::max<int64_t>(need, 32), cap_max);
   cap = (cap + 31) & ~31;
+  // the whole source set of any fan fits one pass <=> no per-ray quotient array
+  int mp = need > cap ? 1 : 0;
   // shrink the per-pass slots until the CTA fits the opt-in shared memory
-  while (cap > 32 && scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent) > (size_t)m->smem_optin)
+  while (cap > 32 && scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent, mp) > (size_t)m->smem_optin) {
     cap = ((cap / 2) + 31) & ~31;
-  if (scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent) > (size_t)m->smem_optin) {
+    mp = 1;
+  }
+  pl.multipass = mp;
+  if (scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent, mp) > (size_t)m->smem_optin) {
     capi_set_error("fan does not fit shared memory (too many rays / object lines per world)");
     return UMRS_ERR_UNSUPPORTED;
   }
@@ -344,6 +350,7 @@ int umrs_scan_batch_device(umrs_map* m, const float* obj_segs_dev, int32_t n_obj
   p.c.cap = pl.cap;
   p.c.max_rows = pl.max_rows;
   p.c.max_rays = num_rays;
+  p.c.multipass = pl.multipass;
   p.c.ranges = ranges_dev;
   p.c.hit_idx = hit_idx_dev;
   p.c.counters = nullptr;

@@ -37,7 +37,10 @@ struct HumanState {
 static_assert(sizeof(HumanState) == 64, "HumanState must be 64 B");
 
 constexpr int kAgeNever = 1 << 28;
-constexpr int kScanThreads = 256;  // 8 warps per fan CTA
+#ifndef UMRS_SCAN_THREADS
+#define UMRS_SCAN_THREADS 256
+#endif
+constexpr int kScanThreads = UMRS_SCAN_THREADS;  // warps per fan CTA x 32
 constexpr int kMaxRays = 16384;    // per fan (bounded by the per-ray best arrays in smem)
 
 // ---- where a fan's candidate segments come from ----------------------------------
@@ -68,6 +71,7 @@ struct ScanCommon {
   int32_t cap;                   // candidate slots per pass (smem sizing)
   int32_t max_rows;              // source rows a fan can touch (smem sizing)
   int32_t max_rays;              // largest num_rays of any fan of the launch (smem sizing)
+  int32_t multipass;             // a fan's source set can exceed cap (keeps best_q in smem)
 };
 
 struct ScanBatchParams {
@@ -112,7 +116,8 @@ struct WorldStepParams {
 };
 
 // Dynamic shared memory of one fan CTA.
-size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent);
+size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent,
+                       int multipass);
 
 cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream);
 cudaError_t launch_world_step(const WorldStepParams& p, cudaStream_t stream);

@@ -30,21 +30,26 @@
 //      is then evaluated with the reference's exact expression
 //   F  finalise: publishLaser post-process (dropout + Philox noise), coalesced
 //      stores of ranges / hit indices
+#include <stdlib.h>
+
 #include "umrs_device.cuh"
 #include "umrs_internal.h"
+
+#ifndef UMRS_MIN_CTAS
+#define UMRS_MIN_CTAS 4   // resident fan CTAs per SM the register budget is held to (64 regs)
+#endif
 
 namespace umrs {
 
 // ---- shared-memory carve-up --------------------------------------------------
 struct SmemView {
-  float4* rec4;      // [cap] S1: translated {p0x,p0y,p1x,p1y}; S2: {a0, a1, nx, ny}
-  float* recc;       // [cap] c = n . p0'
-  int32_t* idx;      // [cap] hit index of the slot (GetSceneLines order)
-  int2* span;        // [cap] conservative ray-index interval {lo, hi}; lo > hi = dead
+  float4* rec;       // [2*cap] slot s = rec[2s], rec[2s+1]:
+                     //   S1: {p0x,p0y,p1x,p1y} translated | {-, hit index, -, -}
+                     //   S2: {a0, a1, nx, ny}             | {c = n . p0', hit index, -, -}
   uint16_t* pool;    // [3*cap] bucket entries (slots): chunk c owns [c*K, (c+1)*K)
-  uint16_t* wide;    // [cap] slots that met a full bucket: span-checked per chunk
+  uint16_t* wide;    // [cap/4] slots of candidates that met a full bucket: span-checked per chunk
   float* best_r;     // [max_rays] range of the running winner (the reference's exact expression)
-  float* best_q;     // [max_rays] the 2-ulp quotient the winner was selected on (pass to pass)
+  float* best_q;     // [max_rays] the quotient the winner was selected on (multi-pass plans only)
   int32_t* best_i;   // [max_rays] its hit index (-1: none)
   int32_t* cnt;      // [n_chunks_max] (wrapping entries << 16) | plain entries of the bucket
   int32_t* start;    // [n_chunks_max] (spare)
@@ -54,22 +59,22 @@ struct SmemView {
   float4* obj;       // [n_obj_lines] world object lines (world step only)
   float* ent;        // [n_ent][5] {x, y, theta, sin, cos} (world step only)
 };
-enum { kCtlNCand = 0, kCtlPoolUsed = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4 };
+enum { kCtlNCand = 0, kCtlWideOverflow = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
 struct SmemOffsets { size_t o[17]; };
 
 __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int max_rays,
-                                                   int n_obj_lines, int n_ent) {
+                                                   int n_obj_lines, int n_ent, int multipass) {
   const size_t n_chunks = (size_t)((max_rays + 31) >> 5);
   const size_t sizes[16] = {
-      sizeof(float4) * (size_t)cap,            // rec4
-      sizeof(float) * (size_t)cap,             // recc
-      sizeof(int32_t) * (size_t)cap,           // idx
-      sizeof(int2) * (size_t)cap,              // span
+      sizeof(float4) * 2 * (size_t)cap,        // rec
+      0,                                       // (spare)
+      0,                                       // (spare)
+      0,                                       // (spare)
       sizeof(uint16_t) * (3 * (size_t)cap > 8 * n_chunks ? 3 * (size_t)cap : 8 * n_chunks),  // pool
-      sizeof(uint16_t) * (size_t)cap,          // wide
+      sizeof(uint16_t) * (size_t)(cap / 4),    // wide
       sizeof(float) * (size_t)max_rays,        // best_r
       sizeof(int32_t) * (size_t)max_rays,      // best_i
       sizeof(int32_t) * n_chunks,              // cnt
@@ -79,7 +84,7 @@ __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int ma
       sizeof(int32_t) * 8,                     // ctl
       sizeof(float4) * (size_t)n_obj_lines,    // obj
       sizeof(float) * 5 * (size_t)n_ent,       // ent
-      sizeof(float) * (size_t)max_rays};       // best_q
+      multipass ? sizeof(float) * (size_t)max_rays : 0};  // best_q
   SmemOffsets L;
   size_t o = 0;
   for (int k = 0; k < 16; ++k) {
@@ -90,18 +95,16 @@ __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int ma
   return L;
 }
 
-size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent) {
-  return smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent).o[16];
+size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent,
+                       int multipass) {
+  return smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent, multipass).o[16];
 }
 
 __device__ inline SmemView carve(unsigned char* base, int cap, int max_rows, int max_rays,
-                                 int n_obj_lines, int n_ent) {
-  const SmemOffsets L = smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent);
+                                 int n_obj_lines, int n_ent, int multipass) {
+  const SmemOffsets L = smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent, multipass);
   SmemView v;
-  v.rec4 = reinterpret_cast<float4*>(base + L.o[0]);
-  v.recc = reinterpret_cast<float*>(base + L.o[1]);
-  v.idx = reinterpret_cast<int32_t*>(base + L.o[2]);
-  v.span = reinterpret_cast<int2*>(base + L.o[3]);
+  v.rec = reinterpret_cast<float4*>(base + L.o[0]);
   v.pool = reinterpret_cast<uint16_t*>(base + L.o[4]);
   v.wide = reinterpret_cast<uint16_t*>(base + L.o[5]);
   v.best_r = reinterpret_cast<float*>(base + L.o[6]);
@@ -213,8 +216,8 @@ __device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
     if (keep) {
       const int pos = base + __popc(m & ((1u << lane) - 1u));
       // translate by -loc (vector_map.cpp:447-448)
-      sm.rec4[pos] = make_float4(s.x - fan.lx, s.y - fan.ly, s.z - fan.lx, s.w - fan.ly);
-      sm.idx[pos] = hit;
+      sm.rec[2 * pos] = make_float4(s.x - fan.lx, s.y - fan.ly, s.z - fan.lx, s.w - fan.ly);
+      sm.rec[2 * pos + 1] = make_float4(0.f, __int_as_float(hit), 0.f, 0.f);
     }
   }
 }
@@ -254,33 +257,37 @@ __device__ __forceinline__ int bucket_capacity(int cap, int n_chunks) {
   return k < 8 ? 8 : (k > 248 ? 248 : k);
 }
 
-// ---- S2: records, spans, buckets ------------------------------------------------------
-__device__ void make_records(const SmemView& sm, const Lattice& L, int K,
+// Conservative ray-index interval of a record (a0 -> a1 counter-clockwise); the
+// exact decision is the float predicate in the ray loop.
+__device__ __forceinline__ int2 span_of(float a0, float a1, const Lattice& L) {
+  if (!L.cull_ok) return make_int2(0, L.num_rays - 1);
+  const float arc = (a0 > a1) ? (a1 + k2PiF) - a0 : a1 - a0;
+  float u0 = a0 - L.amin;
+  u0 -= k2PiF * floorf(u0 / k2PiF);              // [0, 2pi)
+  return make_int2((int)floorf(u0 * L.inv_da) - 2, (int)ceilf((u0 + arc) * L.inv_da) + 2);
+}
+
+// ---- S2: records + buckets ---------------------------------------------------------------
+// A slot that is not a candidate for this fan (dropped by :451, or outside the
+// fan) gets a0 = a1 = NaN: no ray angle compares true against it.
+__device__ void make_records(const SmemView& sm, const Lattice& L, int K, int wide_cap,
                              unsigned long long* counters) {
   const int n_cand = sm.ctl[kCtlNCand];
+  const float nanf_ = __int_as_float(0x7fc00000);
   int n_valid = 0;
   for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
-    const float4 p = sm.rec4[slot];
+    const float4 p = sm.rec[2 * slot];
     const SegCast k = make_cast(p.x, p.y, p.z, p.w, L);
-    int2 sp = make_int2(1, 0);
+    float4 rec = make_float4(nanf_, nanf_, 0.f, 0.f);
     if (k.valid) {
       ++n_valid;
-      if (L.cull_ok) {
-        // Conservative ray-index estimate; the exact decision is the float
-        // predicate in the ray loop.
-        float u0 = k.a0 - L.amin;
-        u0 -= k2PiF * floorf(u0 / k2PiF);              // [0, 2pi)
-        sp.x = (int)floorf(u0 * L.inv_da) - 2;
-        sp.y = (int)ceilf((u0 + k.arc) * L.inv_da) + 2;
-      } else {
-        sp = make_int2(0, L.num_rays - 1);
-      }
+      const int2 sp = span_of(k.a0, k.a1, L);
       const ChunkRanges cr = chunk_ranges(sp.x, sp.y, L);
-      if (cr.xa > cr.xb && cr.ya > cr.yb) {
-        sp = make_int2(1, 0);                          // outside the fan
-      } else {
+      if (cr.xa <= cr.xb || cr.ya <= cr.yb) {
+        rec = make_float4(k.a0, k.a1, k.nx, k.ny);
         const bool wrap = k.a0 > k.a1;
         const int inc = wrap ? 0x10000 : 1;
+        const uint16_t entry = (uint16_t)slot;
         bool spilled = false;
         for (int part = 0; part < 2; ++part) {
           const int ca = part ? cr.ya : cr.xa, cb = part ? cr.yb : cr.xb;
@@ -288,19 +295,22 @@ __device__ void make_records(const SmemView& sm, const Lattice& L, int K,
             const int old = atomicAdd(&sm.cnt[c], inc);
             const int na = old & 0xffff, nb = old >> 16;
             if (na + nb < K) {
-              sm.pool[c * K + (wrap ? K - 1 - nb : na)] = (uint16_t)slot;
+              sm.pool[c * K + (wrap ? K - 1 - nb : na)] = entry;
             } else {
               atomicSub(&sm.cnt[c], inc);   // bucket full: stays full from here on
               spilled = true;
             }
           }
         }
-        if (spilled) sm.wide[atomicAdd(&sm.ctl[kCtlNWide], 1)] = (uint16_t)slot;
+        if (spilled) {
+          const int w = atomicAdd(&sm.ctl[kCtlNWide], 1);
+          if (w < wide_cap) sm.wide[w] = entry;
+          else sm.ctl[kCtlWideOverflow] = 1;   // ray loop falls back to sweeping every slot
+        }
       }
     }
-    sm.rec4[slot] = make_float4(k.a0, k.a1, k.nx, k.ny);
-    sm.recc[slot] = k.c;
-    sm.span[slot] = sp;
+    sm.rec[2 * slot] = rec;
+    reinterpret_cast<float*>(sm.rec + 2 * slot + 1)[0] = k.c;
   }
   if (counters != nullptr) {
     for (int o = 16; o > 0; o >>= 1) n_valid += __shfl_down_sync(0xffffffffu, n_valid, o);
@@ -308,14 +318,57 @@ __device__ void make_records(const SmemView& sm, const Lattice& L, int K,
   }
 }
 
+// 1 / x to 1 ulp, one MUFU.RCP (no denormal-scaling wrapper around it).
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// Shared-memory loads of the hot loop on 32-bit shared addresses (register +
+// immediate), so that no address arithmetic lands on the integer pipe.
+__device__ __forceinline__ float4 lds_f4(unsigned addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds_f1_off16(unsigned addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1+16];" : "=f"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ int lds_i1_off20(unsigned addr) {
+  int v;
+  asm volatile("ld.shared.b32 %0, [%1+20];" : "=r"(v) : "r"(addr));
+  return v;
+}
+template <int kOff>
+__device__ __forceinline__ unsigned lds_u16(unsigned addr) {
+  unsigned v;
+  asm volatile("ld.shared.u16 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(kOff));
+  return v;
+}
+// slot -> shared address of its 32-byte record: one IMAD (float/IMAD pipe).
+__device__ __forceinline__ unsigned rec_addr(unsigned slot, unsigned rec_s) {
+  unsigned a;
+  asm("mad.lo.u32 %0, %1, 32, %2;" : "=r"(a) : "r"(slot), "r"(rec_s));
+  return a;
+}
+
 // ---- C: ray loop ----------------------------------------------------------------------
-__device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, int K, int pass,
-                         unsigned long long* counters) {
+__device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, int K, int wide_cap,
+                         int pass, bool multipass, unsigned long long* counters) {
   const int lane = threadIdx.x & 31;
   const int n_chunks = (fan.num_rays + 31) >> 5;
-  const int n_wide = sm.ctl[kCtlNWide];
+  const int n_cand = sm.ctl[kCtlNCand];
+  // not a proper fan, or more spilled candidates than the wide list holds: sweep every slot
+  const bool sweep_all = !L.cull_ok || sm.ctl[kCtlWideOverflow] != 0;
+  const int n_wide = sweep_all ? 0 : sm.ctl[kCtlNWide];
   unsigned long long n_pairs = 0;
   const float inf = __int_as_float(0x7f800000);
+  const unsigned rec_s = (unsigned)__cvta_generic_to_shared(sm.rec);
+  const unsigned pool_s = (unsigned)__cvta_generic_to_shared(sm.pool);
 
   for (;;) {
     int chunk = 0;
@@ -332,74 +385,101 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
       ray_dir(a, rx, ry);                                // :472
     }
     const int prev_i = (pass > 0 && live) ? sm.best_i[i] : -1;
-    const float prev_q = prev_i >= 0 ? sm.best_q[i] : inf;
-    float best = prev_q;
-    int best_slot = -1;
-    bool tie = false;
+    float best = prev_i >= 0 ? sm.best_q[i] : inf;
+    int best_s = -1;          // slot of the running winner of this pass
+    int tie = 0;   // set when a covering candidate equals the running best (collinear wall pieces
+                   // share n and c exactly, so the equality must be qualified by coverage)
 
-    // One candidate against the 32 rays of the chunk.  The winner is selected on
-    // q = c / (n . r) evaluated with one FMA and the 2-ulp hardware quotient; the
-    // reference's exact expression is evaluated once, for the winner, below.
-    // An equal q is only flagged here; see the careful sweep below.
-#define UMRS_TEST(SLOT, COVER_EXPR)                                              \
-    {                                                                            \
-      const int s_ = (SLOT);                                                     \
-      const float4 r4 = sm.rec4[s_];                  /* broadcast LDS.128 */    \
-      const float den = __fmaf_rn(r4.z, rx, r4.w * ry);                          \
-      const float q = __fdividef(sm.recc[s_], den);                              \
-      const bool cov = (COVER_EXPR);                  /* :469-470 */             \
-      tie = tie || (cov && q == best);                                           \
-      if (cov && q < best) { best = q; best_slot = s_; }                         \
+    // One candidate (slot S) against the 32 rays of the chunk.
+    //  * The winner is selected on q = c / (n . r) evaluated with one FMA and a
+    //    1-ulp reciprocal; the reference's exact expression is evaluated once, for
+    //    the winner, below.  An equal q only raises `tie` (careful sweep below).
+    //  * Coverage (:469-470, inclusive) as the sign of one product, so that it
+    //    costs float-pipe adds instead of integer-pipe compares:
+    //      plain    a0 <= a && a <= a1   <=>   (a - a0) * (a1 - a) >= 0
+    //      wrapping a0 <= a || a <= a1   <=>   (a - a1) * (a0 - a) <= 0
+    //    (a float difference is zero only for equal operands and has the exact
+    //    sign; the product cannot underflow because |a1 - a0| >= 1e-4 and nonzero
+    //    angle differences are >= 1e-9; NaN -- a dead lane -- compares false.)
+#define UMRS_TEST(S, COVER_EXPR)                                                          \
+    {                                                                                     \
+      const int s_ = (int)(S);                                                            \
+      const unsigned ra_ = rec_addr((unsigned)s_, rec_s);                                 \
+      const float4 r4 = lds_f4(ra_);                          /* broadcast LDS.128 */     \
+      const float cc = lds_f1_off16(ra_);                                                 \
+      const float q = cc * rcp_approx(__fmaf_rn(r4.z, rx, r4.w * ry));                    \
+      const bool cov = (COVER_EXPR);                                                      \
+      if (cov && q == best) tie = 1;                                                      \
+      if (cov && q < best) { best = q; best_s = s_; }                                     \
     }
+#define UMRS_COV_PLAIN ((a - r4.x) * (r4.y - a) >= 0.f)
+#define UMRS_COV_WRAP ((a - r4.y) * (r4.x - a) <= 0.f)
 
-    const int packed = sm.cnt[chunk];
-    const int n_plain = packed & 0xffff, n_wrap = packed >> 16;
-    const uint16_t* bucket = sm.pool + chunk * K;
-    {
-      int e = 0;
-      for (; e + 1 < n_plain; e += 2) {               // two candidates in flight
-        const uint32_t two = *reinterpret_cast<const uint32_t*>(bucket + e);
-        UMRS_TEST((int)(two & 0xffffu), r4.x <= a && a <= r4.y)
-        UMRS_TEST((int)(two >> 16), r4.x <= a && a <= r4.y)
+    int n_plain = 0, n_wrap = 0;
+    const unsigned bucket_s = pool_s + 2u * (unsigned)(chunk * K);
+    if (!sweep_all) {
+      const int packed = sm.cnt[chunk];
+      n_plain = packed & 0xffff;
+      n_wrap = packed >> 16;
+      unsigned bp = bucket_s;
+      int n = n_plain;
+      for (; n >= 4; n -= 4, bp += 8) {               // four candidates in flight
+        const unsigned e0 = lds_u16<0>(bp), e1 = lds_u16<2>(bp), e2 = lds_u16<4>(bp), e3 = lds_u16<6>(bp);
+        UMRS_TEST(e0, UMRS_COV_PLAIN)
+        UMRS_TEST(e1, UMRS_COV_PLAIN)
+        UMRS_TEST(e2, UMRS_COV_PLAIN)
+        UMRS_TEST(e3, UMRS_COV_PLAIN)
       }
-      if (e < n_plain) UMRS_TEST((int)bucket[e], r4.x <= a && a <= r4.y)
-    }
-    for (int e = 0; e < n_wrap; ++e) UMRS_TEST((int)bucket[K - 1 - e], r4.x <= a || a <= r4.y)
-    n_pairs += n_plain + n_wrap;
-    for (int e = 0; e < n_wide; ++e) {
-      const int slot = sm.wide[e];
-      const int2 sp = sm.span[slot];
-      if ((sp.x <= ce && sp.y >= cs) || (L.cull_ok && sp.x - L.p_hi <= ce && sp.y - L.p_lo >= cs)) {
-        UMRS_TEST(slot, cast_covers(r4.x, r4.y, a))
-        ++n_pairs;
+      for (; n > 0; --n, bp += 2) UMRS_TEST(lds_u16<0>(bp), UMRS_COV_PLAIN)
+      bp = bucket_s + 2u * (unsigned)(K - 1);
+      for (int e = 0; e < n_wrap; ++e, bp -= 2) UMRS_TEST(lds_u16<0>(bp), UMRS_COV_WRAP)
+      n_pairs += n_plain + n_wrap;
+      for (int e = 0; e < n_wide; ++e) {
+        const int ws = sm.wide[e];
+        const float4 w4 = sm.rec[2 * ws];
+        const int2 sp = span_of(w4.x, w4.y, L);
+        if ((sp.x <= ce && sp.y >= cs) || (sp.x - L.p_hi <= ce && sp.y - L.p_lo >= cs)) {
+          UMRS_TEST(ws, cast_covers(r4.x, r4.y, a))
+          ++n_pairs;
+        }
       }
+    } else {
+      for (int slot = 0; slot < n_cand; ++slot) UMRS_TEST(slot, cast_covers(r4.x, r4.y, a))
+      n_pairs += n_cand;
     }
 #undef UMRS_TEST
+#undef UMRS_COV_PLAIN
+#undef UMRS_COV_WRAP
 
     // Careful sweep, only if some ray of the chunk saw two candidates with the
     // same q: lowest hit index wins (the reference's scan order with a strict <).
-    if (__any_sync(0xffffffffu, tie)) {
-      int best_idx = best_slot >= 0 ? sm.idx[best_slot] : prev_i;
+    if (__any_sync(0xffffffffu, tie != 0)) {
+      int best_idx = best_s >= 0 ? lds_i1_off20(rec_addr((unsigned)best_s, rec_s)) : prev_i;
       auto careful = [&](int slot) {
-        const float4 r4 = sm.rec4[slot];
+        const unsigned ra = rec_addr((unsigned)slot, rec_s);
+        const float4 r4 = lds_f4(ra);
         if (!cast_covers(r4.x, r4.y, a)) return;
-        const float den = __fmaf_rn(r4.z, rx, r4.w * ry);
-        const float q = __fdividef(sm.recc[slot], den);
-        const int id = sm.idx[slot];
-        if (q == best && id < best_idx) { best_slot = slot; best_idx = id; }
+        const float q = lds_f1_off16(ra) * rcp_approx(__fmaf_rn(r4.z, rx, r4.w * ry));
+        const int id = lds_i1_off20(ra);
+        if (q == best && id < best_idx) { best_s = slot; best_idx = id; }
       };
-      for (int e = 0; e < n_plain; ++e) careful(bucket[e]);
-      for (int e = 0; e < n_wrap; ++e) careful(bucket[K - 1 - e]);
-      for (int e = 0; e < n_wide; ++e) careful(sm.wide[e]);
+      if (!sweep_all) {
+        for (int e = 0; e < n_plain; ++e) careful(sm.pool[chunk * K + e]);
+        for (int e = 0; e < n_wrap; ++e) careful(sm.pool[chunk * K + K - 1 - e]);
+        for (int e = 0; e < n_wide; ++e) careful(sm.wide[e]);
+      } else {
+        for (int slot = 0; slot < n_cand; ++slot) careful(slot);
+      }
     }
 
     if (live) {
-      if (best_slot >= 0) {
-        const float4 r4 = sm.rec4[best_slot];
+      if (best_s >= 0) {
+        const unsigned ra = rec_addr((unsigned)best_s, rec_s);
+        const float4 r4 = lds_f4(ra);
         const float den = r4.z * rx + r4.w * ry;         // n.dot(r), vector_map.cpp:473
-        sm.best_r[i] = sm.recc[best_slot] / den;
-        sm.best_q[i] = best;
-        sm.best_i[i] = sm.idx[best_slot];
+        sm.best_r[i] = lds_f1_off16(ra) / den;
+        if (multipass) sm.best_q[i] = best;
+        sm.best_i[i] = lds_i1_off20(ra);
       } else if (pass == 0) {
         sm.best_r[i] = inf;
         sm.best_i[i] = -1;
@@ -464,9 +544,9 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1);
     __syncthreads();
     if (pass == 0 || sm.ctl[kCtlNCand] > 0) {   // block-uniform: a later pass may be empty
-      make_records(sm, L, K, c.counters);
+      make_records(sm, L, K, c.cap / 4, c.counters);
       __syncthreads();
-      ray_loop(sm, fan, L, K, pass, c.counters);
+      ray_loop(sm, fan, L, K, c.cap / 4, pass, c.multipass != 0, c.counters);
     }
     __syncthreads();
     if (v0 + c.cap < v_total) {   // another pass: reset the per-pass state
@@ -480,10 +560,10 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
 }
 
 // ---- scan-only kernel (umrs_predicted_scan / umrs_scan_batch) -------------------
-__global__ void __launch_bounds__(kScanThreads)
+__global__ void __launch_bounds__(kScanThreads, UMRS_MIN_CTAS)
 k_scan_batch(const __grid_constant__ ScanBatchParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const SmemView sm = carve(smem_raw, p.c.cap, p.c.max_rows, p.c.max_rays, 0, 0);
+  const SmemView sm = carve(smem_raw, p.c.cap, p.c.max_rows, p.c.max_rays, 0, 0, p.c.multipass);
   for (int f = blockIdx.x; f < p.n_fans; f += gridDim.x) {
     const float4 fp = __ldg(p.fans + f);
     Fan fan;
@@ -665,11 +745,11 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
 // CTA alone writes the "out" state (ping-pong buffers).  Order as in
 // Simulator::Run (simulator.cpp:531-541): update() first, scan from the
 // post-step pose against the post-step object lines.
-__global__ void __launch_bounds__(kScanThreads)
+__global__ void __launch_bounds__(kScanThreads, UMRS_MIN_CTAS)
 k_world_step(const __grid_constant__ WorldStepParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int n_ent = p.O + p.H + p.R;
-  const SmemView sm = carve(smem_raw, p.c.cap, p.c.max_rows, p.c.max_rays, p.L_obj, n_ent);
+  const SmemView sm = carve(smem_raw, p.c.cap, p.c.max_rows, p.c.max_rays, p.L_obj, n_ent, p.c.multipass);
   const int w = p.world_first + (int)(blockIdx.x / (unsigned)p.R);
   const int r = (int)(blockIdx.x % (unsigned)p.R);
   const bool owner = (r == 0);
@@ -822,7 +902,7 @@ static cudaError_t configure_smem(size_t smem_bytes) {
 
 cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream) {
   if (p.n_fans <= 0) return cudaSuccess;
-  const size_t smem = scan_smem_bytes(p.c.cap, p.c.max_rows, p.c.max_rays, 0, 0);
+  const size_t smem = scan_smem_bytes(p.c.cap, p.c.max_rows, p.c.max_rays, 0, 0, p.c.multipass);
   cudaError_t e = configure_smem(smem);
   if (e != cudaSuccess) return e;
   k_scan_batch<<<p.n_fans, kScanThreads, smem, stream>>>(p);
@@ -833,7 +913,8 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream) {
 cudaError_t launch_world_step(const WorldStepParams& p, cudaStream_t stream) {
   const int fans = p.world_count * p.R;
   if (fans <= 0) return cudaSuccess;
-  const size_t smem = scan_smem_bytes(p.c.cap, p.c.max_rows, p.c.max_rays, p.L_obj, p.O + p.H + p.R);
+  size_t smem = scan_smem_bytes(p.c.cap, p.c.max_rows, p.c.max_rays, p.L_obj, p.O + p.H + p.R, p.c.multipass);
+  if (const char* pad = getenv("UMRS_SMEM_PAD")) smem += (size_t)atoi(pad);  // occupancy experiments
   cudaError_t e = configure_smem(smem);
   if (e != cudaSuccess) return e;
   k_world_step<<<fans, kScanThreads, smem, stream>>>(p);

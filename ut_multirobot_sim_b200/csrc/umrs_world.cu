@@ -19,7 +19,7 @@ struct umrs_map;
 namespace umrs {
 int capi_cuda_fail(cudaError_t e, const char* what);
 void capi_set_error(const char* msg);
-struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; };
+struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; int32_t multipass; };
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
 }  // namespace umrs
@@ -342,6 +342,7 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   p.c.cap = w->plan.cap;
   p.c.max_rows = w->plan.max_rows;
   p.c.max_rays = w->max_rays;
+  p.c.multipass = w->plan.multipass;
   p.c.ranges = w->d_ranges;
   p.c.hit_idx = w->d_idx;
   p.c.counters = w->counters_on ? w->d_counters : nullptr;
