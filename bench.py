@@ -5,8 +5,9 @@
   torchrun ... bench.py --gpus N ...          (one rank per GPU, N > 1)
 
 Workload (BASELINE.json configs):
-  N = 1 : config 3 -- 4096 worlds x 1 Ackermann car x 1081 rays, fused step
-  N > 1 : config 5 -- 65,536 worlds sharded contiguously over the N GPUs
+  every N : BASELINE config 5's per-GPU share -- 8192 worlds x 1 Ackermann car x 1081
+            rays per GPU, contiguous world blocks (65,536 worlds at N = 8; weak scaling);
+            --worlds 4096 gives config 3
 against one shared seeded floor plan of --map-segments (default 1024) cleaned
 segments.  A "step" is one umrs_world_step over all worlds of the rank.
 
@@ -29,6 +30,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_RAYS = 1081
+WORLDS_PER_GPU = 8192  # BASELINE config 5: 65,536 worlds over 8 GPUs (weak scaling at every N)
 EXTENT = 200.0
 FLOPS_PER_TEST = 12.0  # nominal cost of one ray-segment candidate test
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4: SMs x lanes x FMA x max SM clock
@@ -51,22 +53,22 @@ def parse():
 def total_worlds(args):
     if args.worlds:
         return args.worlds
-    return 4096 if args.gpus == 1 else 65536
+    return WORLDS_PER_GPU * max(1, args.gpus)
 
 
 def workload_name(args):
     w = total_worlds(args)
-    tag = "config3" if args.gpus == 1 else "config5"
-    return "%s: %d worlds x 1 Ackermann x %d rays, fused step+scan, floor plan %d segs" % (
-        tag, w, N_RAYS, args.map_segments)
+    return ("config5 shard (65,536 worlds over 8 GPUs = %d per GPU; config3 is --worlds 4096): %d worlds x 1 "
+            "Ackermann x %d rays on %d GPU(s), fused step+scan, floor plan %d segs" % (
+                WORLDS_PER_GPU, w, N_RAYS, max(1, args.gpus), args.map_segments))
 
 
 def make_inputs(args, rank, world_size):
     import ut_multirobot_sim_b200 as umrs
     from ut_multirobot_sim_b200 import synth
+    from ut_multirobot_sim_b200.shard import shard_worlds
     W_total = total_worlds(args)
-    per = W_total // world_size
-    base = rank * per
+    base, per = shard_worlds(W_total, rank, world_size)
     segs = umrs.map_cleanup(synth.floorplan_segments(args.map_segments, extent=EXTENT, seed=1234))
     poses = synth.sample_free_poses_fast(segs, W_total, EXTENT, seed=11)[base:base + per]
     cmds = [synth.ackermann_commands(W_total, 1, s, seed=42)[base:base + per] for s in range(8)]
@@ -114,28 +116,37 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.sm)}
 
 
-def cpu_baseline(segs, fans, range_max, n_fans, threads):
-    """oracle/_ref (the unmodified reference scan) on `threads` host cores."""
+def cpu_baseline(segs, fans, range_max, threads, budget_s):
+    """oracle/_ref (the unmodified reference scan, vector_map.cpp compiled in place) on
+    `threads` host cores: whole passes over `fans` until about budget_s of wall time."""
     from tests import oracle_lib
     ref = oracle_lib.load_ref()
-    kind = "reference"
     if ref is None:
         return None
     rm = ref.map_from_segments(segs, False)
-    f = np.ascontiguousarray(fans[:n_fans], np.float32)
+    f = np.ascontiguousarray(fans, np.float32)
     rm.scan_batch(f[:max(1, threads)], 0.4, range_max, N_RAYS, threads=threads)  # warm
     t0 = time.perf_counter()
-    rm.scan_batch(f, 0.4, range_max, N_RAYS, threads=threads)
-    dt = time.perf_counter() - t0
-    return {"value": n_fans * N_RAYS / dt, "unit": "rays/s", "cores": threads, "kind": kind,
-            "seconds": dt}
+    reps = 0
+    while True:
+        rm.scan_batch(f, 0.4, range_max, N_RAYS, threads=threads)
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt >= budget_s or reps >= 1000:
+            break
+    return {"value": reps * len(f) * N_RAYS / dt, "unit": "rays/s", "cores": threads,
+            "kind": "reference", "seconds": dt, "fans": len(f), "passes": reps}
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU scan on all host cores."""
+    """--impl reference: the reference's own CPU implementation of the path on all host
+    cores -- restated Ackermann tick (oracle port; the model sources need ROS headers)
+    + the UNMODIFIED GetPredictedScan (oracle/_ref) -- on the same workload.  A step is
+    one tick of `S` worlds (S = the whole workload unless --cpu-sample-fans bounds it)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    import ctypes as C
     import ut_multirobot_sim_b200 as umrs
     from ut_multirobot_sim_b200 import synth
     from tests import oracle_lib
@@ -147,42 +158,41 @@ def run_reference(args):
         return
     orc = oracle_lib.load_oracle()
     car = umrs.default_robot("ut_automata")
-    # bounded sample of the same workload: S fans per step
-    S = args.cpu_sample_fans or max(cores * 8, 256)
-    poses = synth.sample_free_poses_fast(segs, total_worlds(args), EXTENT, seed=11)[:S]
+    W_total = total_worlds(args)
+    S = min(W_total, args.cpu_sample_fans or 4096)
+    poses = synth.sample_free_poses_fast(segs, W_total, EXTENT, seed=11)[:S]
     rm = ref.map_from_segments(segs, False)
-    import ctypes as C
-    states = [oracle_lib.RobotState() for _ in range(S)]
-    for s, p in zip(states, poses):
-        orc.lib.orc_robot_init(C.byref(s), oracle_lib._fp(np.ascontiguousarray(p, np.float32)))
+    states = (oracle_lib.RobotState * S)()
+    for k in range(S):
+        orc.lib.orc_robot_init(C.byref(states[k]), oracle_lib._fp(np.ascontiguousarray(poses[k], np.float32)))
+    cmd_sets = [np.ascontiguousarray(synth.ackermann_commands(W_total, 1, s, seed=42)[:S, 0]) for s in range(8)]
+    fans = np.empty((S, 4), np.float32)
 
     def one_step(step):
-        cmds = synth.ackermann_commands(total_worlds(args), 1, step % 8, seed=42)[:S]
-        fans = np.empty((S, 4), np.float32)
-        for i, s in enumerate(states):  # restated kinematic step (ackermann_model.cpp:52-96)
-            c = np.ascontiguousarray(cmds[i, 0], np.float32)
-            orc.lib.orc_robot_command(C.byref(s), C.byref(car), oracle_lib._fp(c))
-            orc.lib.orc_robot_step(C.byref(s), C.byref(car), 0.025, 0.0, 0.0)
-            pose = np.array(list(s.pose), np.float32)
-            o = orc.laser_origin(pose, car.laser.loc_x, car.laser.loc_y)
-            fans[i] = (o[0], o[1], car.laser.angle_min + pose[2], car.laser.angle_max + pose[2])
+        orc.lib.orc_robots_tick(states, S, C.byref(car), oracle_lib._fp(cmd_sets[step % 8]),
+                                0.025, oracle_lib._fp(fans))
         return rm.scan_batch(fans, car.laser.range_min, car.laser.range_max, N_RAYS, threads=cores)
 
-    steps = min(args.steps, 20)
-    warm = min(args.warmup, 3)
+    steps, warm = args.steps, args.warmup
+    # keep the whole run within a few minutes whatever --steps says
+    t0 = time.perf_counter()
+    one_step(0)
+    per = time.perf_counter() - t0
+    steps = max(1, min(steps, int(120.0 / max(per, 1e-6))))
+    warm = max(0, min(warm, 3))
     for s in range(warm):
-        one_step(s)
+        one_step(1 + s)
     t0 = time.perf_counter()
     for s in range(steps):
-        one_step(warm + s)
+        one_step(1 + warm + s)
     dt = time.perf_counter() - t0
     value = S * N_RAYS * steps / dt
-    sample = "%d of %d fans per step, %d steps (requested %d), all %d host threads" % (
-        S, total_worlds(args), steps, args.steps, cores)
+    sample = "%d of %d worlds per step, %d steps (requested %d), all %d host threads" % (
+        S, W_total, steps, args.steps, cores)
     print(json.dumps({
         "impl": "reference", "metric": "lidar_rays_per_sec", "value": value, "unit": "rays/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": dt / steps * 1e3,
-        "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
+        "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args), "sample": sample},
         "env_steps_per_sec": S * steps / dt,
@@ -304,7 +314,7 @@ def run_b200(args):
     out = {
         "metric": "lidar_rays_per_sec", "value": value, "unit": "rays/s",
         "n_gpus": world_size, "steps": K, "warmup": Wm, "ms_per_step": ms_dev / K,
-        "higher_is_better": True, "scaling": "strong" if world_size > 1 else "weak",
+        "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args), "worlds_per_gpu": W,
                    "map_segments": int(len(segs)), "laser_noise": True, "motion_noise": True,
@@ -331,12 +341,12 @@ def run_b200(args):
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
         fans = world.fan_params().reshape(-1, 4)
         cores = os.cpu_count() or 1
-        n_fans = args.cpu_sample_fans or min(W, max(cores * 16, 512))
-        cb = cpu_baseline(segs, fans, car.laser.range_max, n_fans, cores)
+        n_fans = min(W, args.cpu_sample_fans or W)
+        cb = cpu_baseline(segs, fans[:n_fans], car.laser.range_max, cores, 12.0)
         if cb is not None:
-            one = cpu_baseline(segs, fans, car.laser.range_max, min(n_fans, 64), 1)
-            cb["sample"] = "%d of %d fans of the same step, reference GetPredictedScan, %d threads" % (
-                n_fans, W, cores)
+            one = cpu_baseline(segs, fans[:min(n_fans, 512)], car.laser.range_max, 1, 4.0)
+            cb["sample"] = ("%d passes over %d of the %d fans of the last step (%.1f s), unmodified reference "
+                            "GetPredictedScan, %d threads" % (cb["passes"], n_fans, W, cb["seconds"], cores))
             cb["single_thread_value"] = one["value"]
             out["cpu_baseline"] = cb
     if rank == 0:

@@ -473,6 +473,17 @@ void orc_robot_step(orc_robot_state* s, const umrs_robot_params* p, float dt_f,
   if (s->cmd_age < ORC_AGE_NEVER) s->cmd_age += 1;
 }
 
+void orc_robots_tick(orc_robot_state* s, int32_t n, const umrs_robot_params* p,
+                     const float* cmds, float dt, float* fans) {
+  for (int32_t i = 0; i < n; ++i) {
+    orc_robot_command(&s[i], p, cmds + 3 * i);
+    orc_robot_step(&s[i], p, dt, 0.0f, 0.0f);
+    orc_laser_origin(s[i].pose, p->laser.loc_x, p->laser.loc_y, fans + 4 * i);
+    fans[4 * i + 2] = p->laser.angle_min + s[i].pose[2]; /* simulator.cpp:408 */
+    fans[4 * i + 3] = p->laser.angle_max + s[i].pose[2]; /* :409 */
+  }
+}
+
 /* ---- humans and footprints --------------------------------------------------- */
 void orc_human_init(orc_human_state* s, const umrs_human_params* p) {
   /* human_object.cpp:83-85 */

@@ -79,6 +79,13 @@ void orc_robot_command(orc_robot_state* s, const umrs_robot_params* p, const flo
 void orc_robot_step(orc_robot_state* s, const umrs_robot_params* p, float dt,
                     float n1, float n2);
 
+/* n robots of one kind, one tick each (command then Step), and the fan each scan
+ * then uses (simulator.cpp:398-411): fans_out[n][4] = {loc_x, loc_y, angle_min +
+ * theta, angle_max + theta}.  Noise draws are zero.  Batch form of the calls
+ * above for the CPU baseline (no Python in the timed loop). */
+void orc_robots_tick(orc_robot_state* s, int32_t n, const umrs_robot_params* p,
+                     const float* cmds_n3, float dt, float* fans_out_n4);
+
 typedef struct orc_human_state {
   float pose[3], start[3], goal[3];
   float trans_vel[2];

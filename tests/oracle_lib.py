@@ -62,6 +62,9 @@ class Oracle:
         lib.orc_robot_command.argtypes = [C.POINTER(RobotState), C.POINTER(RobotParams), _F]
         lib.orc_robot_step.argtypes = [C.POINTER(RobotState), C.POINTER(RobotParams), C.c_float,
                                        C.c_float, C.c_float]
+        lib.orc_robots_tick.restype = None
+        lib.orc_robots_tick.argtypes = [C.POINTER(RobotState), C.c_int32, C.POINTER(RobotParams), _F,
+                                        C.c_float, _F]
         lib.orc_human_init.argtypes = [C.POINTER(HumanState), C.POINTER(HumanParams)]
         lib.orc_human_step.argtypes = [C.POINTER(HumanState), C.POINTER(HumanParams), C.c_float]
         lib.orc_human_template.argtypes = [C.POINTER(HumanParams), _F]

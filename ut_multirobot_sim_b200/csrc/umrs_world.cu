@@ -3,6 +3,7 @@
 // independent worlds in lockstep.  Device state is ping-ponged between two
 // buffers so that the fan CTAs of one world can all read the old state.
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -30,6 +31,8 @@ int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t ma
     if (e__ != cudaSuccess) return capi_cuda_fail(e__, #call);   \
   } while (0)
 
+constexpr int kMaxSlices = 16;
+
 struct umrs_world {
   umrs_world_desc desc;
   std::vector<umrs_robot_params> robots;
@@ -40,6 +43,8 @@ struct umrs_world {
   int32_t L_obj = 0, rays_per_world = 0;
   std::vector<int32_t> ent_off, ray_off, num_rays;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;   // device->host copies of finished slices
+  cudaEvent_t slice_done[kMaxSlices] = {};
   uint64_t step = 0;
   int cur = 0;  // index of the "in" state buffer
   // device
@@ -81,6 +86,9 @@ int umrs_world_destroy(umrs_world* w) {
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (w->stream) cudaStreamDestroy(w->stream);
+  if (w->copy_stream) cudaStreamDestroy(w->copy_stream);
+  for (cudaEvent_t e : w->slice_done)
+    if (e) cudaEventDestroy(e);
   delete w;
   return UMRS_OK;
 }
@@ -174,6 +182,9 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   const size_t n_rays = (size_t)w->W * w->rays_per_world;
   cudaError_t e = cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking);
   auto ok = [&]() { return e == cudaSuccess; };
+  if (ok()) e = cudaStreamCreateWithFlags(&w->copy_stream, cudaStreamNonBlocking);
+  for (int k = 0; k < kMaxSlices; ++k)
+    if (ok()) e = cudaEventCreateWithFlags(&w->slice_done[k], cudaEventDisableTiming);
   if (ok()) e = dalloc(&w->d_robots, (size_t)w->R);
   if (ok()) e = dalloc(&w->d_humans, (size_t)w->H);
   if (ok()) e = dalloc(&w->d_tmpl, (size_t)w->L_obj);
@@ -334,8 +345,10 @@ int umrs_world_get_object_lines(umrs_world* w, float* segs) {
 }  // extern "C"
 
 // ================================== stepping ========================================
+// Launches worlds [first, first + count) of the current tick; `last` closes the tick
+// (state buffers flip, step counter advances).
 static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mask_dev,
-                        cudaStream_t stream) {
+                        cudaStream_t stream, int32_t first, int32_t count, bool last) {
   WorldStepParams p;
   memset(&p, 0, sizeof(p));
   p.c.src = w->plan.src;
@@ -347,7 +360,7 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   p.c.hit_idx = w->d_idx;
   p.c.counters = w->counters_on ? w->d_counters : nullptr;
   p.W = w->W; p.R = w->R; p.H = w->H; p.O = w->O;
-  p.world_first = 0; p.world_count = w->W;
+  p.world_first = first; p.world_count = count;
   p.robots = w->d_robots;
   p.humans = w->d_humans;
   p.tmpl = w->d_tmpl;
@@ -375,11 +388,13 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   p.world_base = w->desc.world_index_base;
   p.laser_noise = w->desc.laser_noise_enabled;
   p.motion_noise = w->desc.motion_noise_enabled;
-  if (w->counters_on)
+  if (w->counters_on && first == 0)
     UMRS_CUDA(cudaMemsetAsync(w->d_counters, 0, sizeof(unsigned long long) * 4, stream));
   UMRS_CUDA(launch_world_step(p, stream));
-  w->cur ^= 1;
-  w->step += 1;
+  if (last) {
+    w->cur ^= 1;
+    w->step += 1;
+  }
   return UMRS_OK;
 }
 
@@ -388,7 +403,7 @@ extern "C" {
 int umrs_world_step_device(umrs_world* w, const float* cmds_dev, const uint8_t* mask_dev,
                            void* stream) {
   if (w == NULL) return UMRS_ERR_INVALID;
-  return world_launch(w, cmds_dev, mask_dev, stream ? (cudaStream_t)stream : w->stream);
+  return world_launch(w, cmds_dev, mask_dev, stream ? (cudaStream_t)stream : w->stream, 0, w->W, true);
 }
 
 int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
@@ -396,18 +411,39 @@ int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
   if (w == NULL) return UMRS_ERR_INVALID;
   if (hit_idx_out != NULL && w->d_idx == NULL) return UMRS_ERR_INVALID;
   const size_t WR = (size_t)w->W * w->R;
-  const size_t n_rays = (size_t)w->W * w->rays_per_world;
   if (cmds)
     UMRS_CUDA(cudaMemcpyAsync(w->d_cmds, cmds, sizeof(float) * WR * 3, cudaMemcpyHostToDevice, w->stream));
   if (cmds && cmd_mask)
     UMRS_CUDA(cudaMemcpyAsync(w->d_mask, cmd_mask, WR, cudaMemcpyHostToDevice, w->stream));
-  int st = world_launch(w, cmds ? w->d_cmds : nullptr, (cmds && cmd_mask) ? w->d_mask : nullptr, w->stream);
-  if (st != UMRS_OK) return st;
-  if (ranges_out)
-    UMRS_CUDA(cudaMemcpyAsync(ranges_out, w->d_ranges, sizeof(float) * n_rays, cudaMemcpyDeviceToHost, w->stream));
-  if (hit_idx_out)
-    UMRS_CUDA(cudaMemcpyAsync(hit_idx_out, w->d_idx, sizeof(int32_t) * n_rays, cudaMemcpyDeviceToHost, w->stream));
+  // The tick is cut into world slices: the device->host copy of slice k runs on the
+  // copy stream while slice k+1 computes, so the call costs ~max(kernel, PCIe)
+  // instead of their sum.  Worlds are independent, so slicing changes nothing else.
+  const float* dc = cmds ? w->d_cmds : nullptr;
+  const uint8_t* dm = (cmds && cmd_mask) ? w->d_mask : nullptr;
+  int n_slices = 1;
+  if (ranges_out != NULL && w->W >= 1024) n_slices = 8;
+  if (const char* e = getenv("UMRS_STEP_SLICES")) n_slices = atoi(e) > 0 ? atoi(e) : 1;
+  if (n_slices > w->W) n_slices = w->W;
+  if (n_slices > kMaxSlices) n_slices = kMaxSlices;
+  const size_t rpw = (size_t)w->rays_per_world;
+  for (int s = 0; s < n_slices; ++s) {
+    const int32_t first = (int32_t)((int64_t)w->W * s / n_slices);
+    const int32_t end = (int32_t)((int64_t)w->W * (s + 1) / n_slices);
+    int st = world_launch(w, dc, dm, w->stream, first, end - first, s == n_slices - 1);
+    if (st != UMRS_OK) return st;
+    if (ranges_out == NULL && hit_idx_out == NULL) continue;
+    UMRS_CUDA(cudaEventRecord(w->slice_done[s], w->stream));
+    UMRS_CUDA(cudaStreamWaitEvent(w->copy_stream, w->slice_done[s], 0));
+    const size_t off = (size_t)first * rpw, cnt = (size_t)(end - first) * rpw;
+    if (ranges_out)
+      UMRS_CUDA(cudaMemcpyAsync(ranges_out + off, w->d_ranges + off, sizeof(float) * cnt,
+                                cudaMemcpyDeviceToHost, w->copy_stream));
+    if (hit_idx_out)
+      UMRS_CUDA(cudaMemcpyAsync(hit_idx_out + off, w->d_idx + off, sizeof(int32_t) * cnt,
+                                cudaMemcpyDeviceToHost, w->copy_stream));
+  }
   UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
   return UMRS_OK;
 }
 
