@@ -1,0 +1,41 @@
+// Drives include/umrs_vector_map.hpp the way Simulator::init / publishLaser drive
+// the reference's VectorMap (simulator.cpp:173, 405-411).  Usage:
+//   adapter_demo <map.txt> <x> <y> <range_max> <angle_min> <angle_max> <num_rays> [obj x0 y0 x1 y1]...
+// prints one range per line (%.9g).  Exit code 3 = the library reported an error.
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "umrs_vector_map.hpp"
+
+struct Vec2 {
+  float x_, y_;
+  Vec2() : x_(0), y_(0) {}
+  Vec2(float x, float y) : x_(x), y_(y) {}
+  float x() const { return x_; }
+  float y() const { return y_; }
+};
+struct Line {
+  Vec2 p0, p1;
+  Line(const Vec2& a, const Vec2& b) : p0(a), p1(b) {}
+};
+
+int main(int argc, char** argv) {
+  if (argc < 8) return 2;
+  try {
+    umrs::VectorMapT<Vec2, Line> map_;
+    map_.Load(argv[1]);
+    for (int k = 8; k + 3 < argc; k += 4)
+      map_.object_lines.push_back(Line(Vec2(atof(argv[k]), atof(argv[k + 1])),
+                                       Vec2(atof(argv[k + 2]), atof(argv[k + 3]))));
+    std::vector<float> ranges;
+    map_.GetPredictedScan(Vec2(atof(argv[2]), atof(argv[3])), 0.4f, atof(argv[4]), atof(argv[5]),
+                          atof(argv[6]), atoi(argv[7]), &ranges);
+    std::printf("lines %zu\n", map_.lines.size());
+    for (float r : ranges) std::printf("%.9g\n", r);
+  } catch (const std::exception& e) {
+    std::fprintf(stderr, "%s\n", e.what());
+    return 3;
+  }
+  return 0;
+}
