@@ -263,6 +263,11 @@ int umrs_world_enable_counters(umrs_world* world, int32_t on);
 int umrs_world_read_counters(umrs_world* world, uint64_t* ray_seg_tests,
                              uint64_t* segs_prepared, uint64_t* chunk_seg_pairs);
 
+/* All eight counters of the last step: {ray_seg_tests, segs_prepared,
+ * chunk_seg_pairs, passes (summed over fans), tie sweeps, spilled-candidate
+ * list entries, fans that swept every slot, spare}. */
+int umrs_world_read_counters_ex(umrs_world* world, uint64_t out8[8]);
+
 /* K3: per-shard statistics of the last step's ranges (count of hits, min, max,
  * sum), reduced on the device; 4 doubles out.  Host buffer. */
 int umrs_world_stats(umrs_world* world, double* out4);

@@ -254,3 +254,22 @@ def test_grid_kernel_with_long_segments_and_far_poses(oracle):
         check_against_tierb(oracle, segs, None, f, 60.0, 541, r[k], i[k])
     assert np.all(r[-1] == np.float32(60.0)) and np.all(i[-1] == -1)
     assert (i[:10] < 5).any() and (i[:10] >= 5).any()   # both long walls and blocks are hit
+
+
+@pytest.mark.parametrize("n_walls", [100, 400], ids=["spill_list", "sweep_every_slot"])
+def test_bucket_overflow_paths(oracle, n_walls):
+    """Many candidates behind one another inside a few 32-ray chunks: more than a
+    bucket holds (they spill to the span-checked list; with 400 also more than that
+    list holds, so the ray loop sweeps every slot).  Same answers either way, incl.
+    the duplicated tests of a candidate that sits in a bucket AND the spill list."""
+    k = np.arange(n_walls, dtype=np.float32)
+    # short walls at x = 3 + 0.05 k, each spanning y in [-0.3, 0.3] (plus a few long ones)
+    segs = np.stack([3 + 0.05 * k, -0.3 + 0 * k, 3 + 0.05 * k, 0.3 + 0 * k], 1).astype(np.float32)
+    segs = np.concatenate([segs, np.array([[-5, -9, 30, -9], [30, -9, 30, 9], [30, 9, -5, 9], [-5, 9, -5, -9]],
+                                          np.float32)])
+    vmap = umrs.VectorMap(lines=segs)
+    for loc, th in (((0.0, 0.0), 0.0), ((1.0, 0.1), 0.05), ((2.9, 0.0), 3.0), ((10.0, 0.05), 3.1)):
+        f = np.array([loc[0], loc[1], np.float32(-2.356) + np.float32(th), np.float32(2.356) + np.float32(th)],
+                     np.float32)
+        r, i = vmap.GetPredictedScan(f[:2], 0.4, 100.0, f[2], f[3], 1081, return_index=True)
+        check_against_tierb(oracle, segs, None, f, 100.0, 1081, r, i)

@@ -119,6 +119,7 @@ SIGNATURES = {
     "umrs_world_enable_counters": (C.c_int, [_P, C.c_int32]),
     "umrs_world_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                            C.POINTER(C.c_uint64)]),
+    "umrs_world_read_counters_ex": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "umrs_world_stats": (C.c_int, [_P, C.POINTER(C.c_double)]),
     "umrs_philox4x32": (None, [C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
                                C.POINTER(C.c_uint32)]),

@@ -247,7 +247,10 @@ class World:
     def read_counters(self):
         a, b, c = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
         check(self._lib.umrs_world_read_counters(self._h, C.byref(a), C.byref(b), C.byref(c)), "read_counters")
-        return {"ray_seg_tests": a.value, "segs_prepared": b.value, "chunk_seg_pairs": c.value}
+        ex = (C.c_uint64 * 8)()
+        check(self._lib.umrs_world_read_counters_ex(self._h, ex), "read_counters_ex")
+        return {"ray_seg_tests": a.value, "segs_prepared": b.value, "chunk_seg_pairs": c.value,
+                "passes": ex[3], "tie_sweeps": ex[4], "spilled_entries": ex[5], "sweep_all_fans": ex[6]}
 
     def stats(self):
         out = (C.c_double * 4)()

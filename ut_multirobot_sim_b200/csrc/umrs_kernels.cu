@@ -47,7 +47,7 @@ struct SmemView {
                      //   S1: {p0x,p0y,p1x,p1y} translated | {-, hit index, -, -}
                      //   S2: {a0, a1, nx, ny}             | {c = n . p0', hit index, -, -}
   uint16_t* pool;    // [3*cap] bucket entries (slots): chunk c owns [c*K, (c+1)*K)
-  uint16_t* wide;    // [cap/4] slots of candidates that met a full bucket: span-checked per chunk
+  uint16_t* wide;    // [cap/2] slots of candidates that met a full bucket: span-checked per chunk
   float* best_r;     // [max_rays] range of the running winner (the reference's exact expression)
   float* best_q;     // [max_rays] the quotient the winner was selected on (multi-pass plans only)
   int32_t* best_i;   // [max_rays] its hit index (-1: none)
@@ -63,6 +63,12 @@ enum { kCtlNCand = 0, kCtlWideOverflow = 1, kCtlNWide = 2, kCtlNextChunk = 3, kC
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
+// Bucket pool: 3 entries per slot, but never less than 48 per chunk of the widest fan.
+__host__ __device__ inline size_t pool_entries(int cap, int n_chunks_max) {
+  const size_t a = 3 * (size_t)cap, b = 48 * (size_t)n_chunks_max;
+  return a > b ? a : b;
+}
+
 struct SmemOffsets { size_t o[17]; };
 
 __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int max_rays,
@@ -73,8 +79,8 @@ __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int ma
       0,                                       // (spare)
       0,                                       // (spare)
       0,                                       // (spare)
-      sizeof(uint16_t) * (3 * (size_t)cap > 8 * n_chunks ? 3 * (size_t)cap : 8 * n_chunks),  // pool
-      sizeof(uint16_t) * (size_t)(cap / 4),    // wide
+      sizeof(uint16_t) * pool_entries(cap, (int)n_chunks),  // pool
+      sizeof(uint16_t) * (size_t)(cap / 2),    // wide
       sizeof(float) * (size_t)max_rays,        // best_r
       sizeof(int32_t) * (size_t)max_rays,      // best_i
       sizeof(int32_t) * n_chunks,              // cnt
@@ -252,9 +258,9 @@ __device__ __forceinline__ ChunkRanges chunk_ranges(int lo, int hi, const Lattic
 // A candidate that meets a full bucket goes to the `wide` list instead, which
 // the ray loop span-checks per chunk (it may then be tested twice in chunks that
 // had room -- harmless for a minimum).
-__device__ __forceinline__ int bucket_capacity(int cap, int n_chunks) {
-  int k = ((3 * cap) / n_chunks) & ~7;
-  return k < 8 ? 8 : (k > 248 ? 248 : k);
+__device__ __forceinline__ int bucket_capacity(int cap, int n_chunks_max, int n_chunks) {
+  const int k = (int)(pool_entries(cap, n_chunks_max) / (size_t)n_chunks) & ~7;
+  return k > 248 ? 248 : k;   // >= 48 by construction of the pool
 }
 
 // Conservative ray-index interval of a record (a0 -> a1 counter-clockwise); the
@@ -454,6 +460,7 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
     // Careful sweep, only if some ray of the chunk saw two candidates with the
     // same q: lowest hit index wins (the reference's scan order with a strict <).
     if (__any_sync(0xffffffffu, tie != 0)) {
+      if (counters != nullptr && lane == 0) atomicAdd(counters + 4, 1ull);
       int best_idx = best_s >= 0 ? lds_i1_off20(rec_addr((unsigned)best_s, rec_s)) : prev_i;
       auto careful = [&](int slot) {
         const unsigned ra = rec_addr((unsigned)slot, rec_s);
@@ -485,6 +492,10 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
         sm.best_i[i] = -1;
       }
     }
+  }
+  if (counters != nullptr && threadIdx.x == 0) {
+    if (n_wide) atomicAdd(counters + 5, (unsigned long long)n_wide);
+    if (sweep_all) atomicAdd(counters + 6, 1ull);
   }
   if (counters != nullptr && lane == 0 && n_pairs) {
     atomicAdd(counters + 2, n_pairs);
@@ -532,7 +543,7 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
                          float* ranges, int32_t* hit_idx, const PostProcess& post) {
   const Lattice L = make_lattice(fan.amin, fan.amax, fan.num_rays);
   const int n_chunks = (fan.num_rays + 31) >> 5;
-  const int K = bucket_capacity(c.cap, n_chunks);
+  const int K = bucket_capacity(c.cap, (c.max_rays + 31) >> 5, n_chunks);
   if (threadIdx.x == 0) build_rows(sm, c.src, fan, n_obj, c.max_rows);
   if (threadIdx.x >= 32 && threadIdx.x < 36) sm.ctl[threadIdx.x - 32] = 0;
   for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) sm.cnt[k] = 0;
@@ -544,9 +555,9 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1);
     __syncthreads();
     if (pass == 0 || sm.ctl[kCtlNCand] > 0) {   // block-uniform: a later pass may be empty
-      make_records(sm, L, K, c.cap / 4, c.counters);
+      make_records(sm, L, K, c.cap / 2, c.counters);
       __syncthreads();
-      ray_loop(sm, fan, L, K, c.cap / 4, pass, c.multipass != 0, c.counters);
+      ray_loop(sm, fan, L, K, c.cap / 2, pass, c.multipass != 0, c.counters);
     }
     __syncthreads();
     if (v0 + c.cap < v_total) {   // another pass: reset the per-pass state
