@@ -36,6 +36,18 @@ FLOPS_PER_TEST = 12.0  # nominal cost of one ray-segment candida
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4: SMs x lanes x FMA x max SM clock
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The result line, on the real stdout."""
+    data = (line + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line + "\n")
+    else:
+        os.write(_JSON_FD, data)
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -154,7 +166,7 @@ def run_reference(args):
     segs = umrs.map_cleanup(synth.floorplan_segments(args.map_segments, extent=EXTENT, seed=1234))
     ref = oracle_lib.load_ref()
     if ref is None:
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libumrs_ref.so not built"}))
+        emit(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libumrs_ref.so not built"}))
         return
     orc = oracle_lib.load_oracle()
     car = umrs.default_robot("ut_automata")
@@ -189,7 +201,7 @@ def run_reference(args):
     value = S * N_RAYS * steps / dt
     sample = "%d of %d worlds per step, %d steps (requested %d), all %d host threads" % (
         S, W_total, steps, args.steps, cores)
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": "lidar_rays_per_sec", "value": value, "unit": "rays/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": dt / steps * 1e3,
         "higher_is_better": True, "scaling": "weak",
@@ -321,8 +333,8 @@ def run_b200(args):
                    "l2": "none" if flush is None else "flushed between timed steps (256 MiB memset outside the event pairs)",
                    "timing": "sum of per-step CUDA-event pairs on the launch stream, max over ranks"},
         "env_steps_per_sec": W * world_size * K / (ms_dev * 1e-3),
-        "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K,
+        "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": h2d * world_size,
+                "d2h_bytes_per_step": d2h * world_size, "ms_per_step": ms_e2e / K,
                 "env_steps_per_sec": W * world_size * K / (ms_e2e * 1e-3)},
         "gpu_launches": int(launches),
         "clocks": clocks,
@@ -350,13 +362,18 @@ def run_b200(args):
             cb["single_thread_value"] = one["value"]
             out["cpu_baseline"] = cb
     if rank == 0:
-        print(json.dumps(out))
+        emit(json.dumps(out))
     if world_size > 1:
         dist.destroy_process_group()
 
 
 def main():
     args = parse()
+    # stdout carries exactly ONE JSON line: anything a library prints there while we run
+    # (NCCL's version banner, ...) is sent to stderr instead
+    global _JSON_FD
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
