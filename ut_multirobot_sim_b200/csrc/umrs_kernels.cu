@@ -52,14 +52,15 @@ struct SmemView {
   float* best_q;     // [max_rays] the quotient the winner was selected on (multi-pass plans only)
   int32_t* best_i;   // [max_rays] its hit index (-1: none)
   int32_t* cnt;      // [n_chunks_max] (wrapping entries << 16) | plain entries of the bucket
-  int32_t* start;    // [n_chunks_max] (spare)
+  uint32_t* zmax2;   // [n_chunks_max] float bits: squared distance beyond which nothing in the chunk can win
   int32_t* row_v0;   // [max_rows + 1] first virtual index of source row r
   int32_t* row_s0;   // [max_rows] first source index of row r (object row: 0)
-  int32_t* ctl;      // [8] n_cand, pool_used, n_wide, next_chunk, n_rows, ...
+  int32_t* ctl;      // [16] n_cand, wide overflow, n_wide, next_chunk, n_rows, wedge flag, -, -, wedge[4]
   float4* obj;       // [n_obj_lines] world object lines (world step only)
   float* ent;        // [n_ent][5] {x, y, theta, sin, cos} (world step only)
 };
-enum { kCtlNCand = 0, kCtlWideOverflow = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4 };
+enum { kCtlNCand = 0, kCtlWideOverflow = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4,
+       kCtlWedgeOn = 5, kCtlWedge = 8 /* 4 floats: e1x, e1y, e2x, e2y */ };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
@@ -84,10 +85,10 @@ __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int ma
       sizeof(float) * (size_t)max_rays,        // best_r
       sizeof(int32_t) * (size_t)max_rays,      // best_i
       sizeof(int32_t) * n_chunks,              // cnt
-      sizeof(int32_t) * n_chunks,              // start
+      sizeof(uint32_t) * n_chunks,             // zmax2
       sizeof(int32_t) * (size_t)(max_rows + 1),  // row_v0
       sizeof(int32_t) * (size_t)(max_rows + 1),  // row_s0
-      sizeof(int32_t) * 8,                     // ctl
+      sizeof(int32_t) * 16,                    // ctl
       sizeof(float4) * (size_t)n_obj_lines,    // obj
       sizeof(float) * 5 * (size_t)n_ent,       // ent
       multipass ? sizeof(float) * (size_t)max_rays : 0};  // best_q
@@ -116,7 +117,7 @@ __device__ inline SmemView carve(unsigned char* base, int cap, int max_rows, int
   v.best_r = reinterpret_cast<float*>(base + L.o[6]);
   v.best_i = reinterpret_cast<int32_t*>(base + L.o[7]);
   v.cnt = reinterpret_cast<int32_t*>(base + L.o[8]);
-  v.start = reinterpret_cast<int32_t*>(base + L.o[9]);
+  v.zmax2 = reinterpret_cast<uint32_t*>(base + L.o[9]);
   v.row_v0 = reinterpret_cast<int32_t*>(base + L.o[10]);
   v.row_s0 = reinterpret_cast<int32_t*>(base + L.o[11]);
   v.ctl = reinterpret_cast<int32_t*>(base + L.o[12]);
@@ -182,6 +183,8 @@ __device__ void build_rows(const SmemView& sm, const MapSource& src, const Fan& 
   sm.ctl[kCtlNRows] = r;
 }
 
+constexpr float kWedgeMargin = 1e-3f;   // rad; dominates every rounding in the wedge test by 1000x
+
 // ---- S1: gather + AABB cull + compaction ------------------------------------------
 // Virtual indices [v_begin, v_end) of this pass.  Object lines [skip_lo, skip_hi)
 // are the fan's own body.
@@ -189,6 +192,13 @@ __device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
                        const float4* obj_segs, int skip_lo, int skip_hi, int v_begin, int v_end) {
   const int n_rows = sm.ctl[kCtlNRows];
   const int lane = threadIdx.x & 31;
+  // Back-wedge cull (fans wider than half a turn): the directions no ray of the fan
+  // takes form a convex wedge; a segment with both (translated) end points inside
+  // the wedge, contracted by 1e-3 rad at both edges, lies inside it entirely, so
+  // no ray angle can satisfy the reference's a0 <= a <= a1 (:469-470) for it.
+  const bool wedge_on = sm.ctl[kCtlWedgeOn] != 0;
+  const float* wf = reinterpret_cast<const float*>(sm.ctl + kCtlWedge);
+  const float e1x = wf[0], e1y = wf[1], e2x = wf[2], e2y = wf[3];
   // iterate in warp-uniform trip counts so that the ballots are full-warp
   for (int vb = v_begin + (int)(threadIdx.x & ~31u); vb < v_end; vb += blockDim.x) {
     const int v = vb + lane;
@@ -214,6 +224,13 @@ __device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
         keep = true;
       }
       keep = keep && aabb_keep(s, fan.lx, fan.ly, fan.range_max);
+      if (wedge_on) {
+        const float ax = s.x - fan.lx, ay = s.y - fan.ly, bx = s.z - fan.lx, by = s.w - fan.ly;
+        // cross(e1, p) > 0 && cross(p, e2) > 0 for p = a, b (NaN compares false: kept)
+        const bool in_a = __fmaf_rn(e1x, ay, -(e1y * ax)) > 0.f && __fmaf_rn(ax, e2y, -(ay * e2x)) > 0.f;
+        const bool in_b = __fmaf_rn(e1x, by, -(e1y * bx)) > 0.f && __fmaf_rn(bx, e2y, -(by * e2x)) > 0.f;
+        keep = keep && !(in_a && in_b);
+      }
     }
     const unsigned m = __ballot_sync(0xffffffffu, keep);
     int base = 0;
@@ -274,53 +291,119 @@ __device__ __forceinline__ int2 span_of(float a0, float a1, const Lattice& L) {
 }
 
 // ---- S2: records + buckets ---------------------------------------------------------------
+// Two sub-phases with a barrier between them:
+//   S2a make_records: per survivor, the record {a0,a1,nx,ny | c, idx, chunk ranges,
+//       mind2}; a well-conditioned candidate lowers zmax2[c] of every chunk whose 32
+//       rays it certainly covers to its farthest end point (squared);
+//   S2b fill_buckets: the candidate enters the bucket of chunk c unless its nearest
+//       point is farther than zmax2[c] -- it then loses on every ray of the chunk.
 // A slot that is not a candidate for this fan (dropped by :451, or outside the
 // fan) gets a0 = a1 = NaN: no ray angle compares true against it.
-__device__ void make_records(const SmemView& sm, const Lattice& L, int K, int wide_cap,
-                             unsigned long long* counters) {
+//
+// Occlusion cull, exactness.  For a ray covered by candidate Y (:469-470) the
+// range c/(n.r) is the distance to a point of segment Y, so <= maxd(Y); for a ray
+// covered by X it is >= mind(X).  Both hold for the FLOAT quotients to 3e-5
+// relative when |n.r| >= 0.01, which |c| > 0.01 maxd guarantees ("well
+// conditioned": |n.r| = |c| / range >= |c| / maxd); others neither occlude nor
+// get culled.  X is dropped from chunk c only if mind2(X) > 1.001 zmax2[c], i.e.
+// mind(X) > 1.0005 maxd(Y) for a Y covering all rays of the chunk: X's quotient
+// is strictly larger than Y's on every ray, so neither the minimum nor a tie can
+// involve X.
+constexpr float kOcclWell = 1e-4f;     // c^2 > kOcclWell * maxd^2
+constexpr float kOcclMargin = 1.001f;  // on squared distances
+
+// chunk ranges -> 30 bits: xa | xb << 10 | (yb + 1) << 20 (ya == 0 whenever the
+// image range exists: lo < period; 0 = no image); n_chunks <= 512.
+__device__ __forceinline__ int pack_ranges(const ChunkRanges& c) {
+  const int y = (c.ya <= c.yb) ? c.yb + 1 : 0;
+  return c.xa | (c.xb << 10) | (y << 20);
+}
+
+// chunks whose rays all lie in the index interval [li, hi] (certain coverage)
+__device__ __forceinline__ void lower_zmax(const SmemView& sm, int li, int hi, int last, int n_chunks,
+                                           uint32_t bits) {
+  const int ca = li > 0 ? (li + 31) >> 5 : 0;
+  const int cb = hi >= last ? n_chunks - 1 : ((hi + 1) >> 5) - 1;
+  for (int c = ca; c <= cb; ++c) atomicMin(&sm.zmax2[c], bits);
+}
+
+__device__ void make_records(const SmemView& sm, const Lattice& L, unsigned long long* counters) {
   const int n_cand = sm.ctl[kCtlNCand];
   const float nanf_ = __int_as_float(0x7fc00000);
+  const int last = L.num_rays - 1, n_chunks = (L.num_rays + 31) >> 5;
   int n_valid = 0;
   for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
     const float4 p = sm.rec[2 * slot];
     const SegCast k = make_cast(p.x, p.y, p.z, p.w, L);
     float4 rec = make_float4(nanf_, nanf_, 0.f, 0.f);
+    int packed = 0;
+    float mind2 = 0.f;
     if (k.valid) {
       ++n_valid;
       const int2 sp = span_of(k.a0, k.a1, L);
       const ChunkRanges cr = chunk_ranges(sp.x, sp.y, L);
       if (cr.xa <= cr.xb || cr.ya <= cr.yb) {
         rec = make_float4(k.a0, k.a1, k.nx, k.ny);
-        const bool wrap = k.a0 > k.a1;
-        const int inc = wrap ? 0x10000 : 1;
-        const uint16_t entry = (uint16_t)slot;
-        bool spilled = false;
-        for (int part = 0; part < 2; ++part) {
-          const int ca = part ? cr.ya : cr.xa, cb = part ? cr.yb : cr.xb;
-          for (int c = ca; c <= cb; ++c) {
-            const int old = atomicAdd(&sm.cnt[c], inc);
-            const int na = old & 0xffff, nb = old >> 16;
-            if (na + nb < K) {
-              sm.pool[c * K + (wrap ? K - 1 - nb : na)] = entry;
-            } else {
-              atomicSub(&sm.cnt[c], inc);   // bucket full: stays full from here on
-              spilled = true;
-            }
+        packed = pack_ranges(cr);
+        if (L.lazy_ok) {
+          const float maxd2 = fmaxf(__fmaf_rn(p.x, p.x, p.y * p.y), __fmaf_rn(p.z, p.z, p.w * p.w));
+          const float c2 = k.c * k.c;
+          if (c2 > kOcclWell * maxd2) {   // well conditioned (NaN: false)
+            // along-line coordinates of the end points; direction d = (ny, -nx)
+            const float t0 = __fmaf_rn(p.x, k.ny, -(p.y * k.nx));
+            const float t1 = __fmaf_rn(p.z, k.ny, -(p.w * k.nx));
+            mind2 = c2 + ((t0 * t1 > 0.f) ? fminf(t0 * t0, t1 * t1) : 0.f);
+            const uint32_t bits = __float_as_uint(maxd2);
+            lower_zmax(sm, sp.x + 4, sp.y - 4, last, n_chunks, bits);
+            lower_zmax(sm, sp.x + 4 - L.p_lo, sp.y - 4 - L.p_hi, last, n_chunks, bits);
           }
-        }
-        if (spilled) {
-          const int w = atomicAdd(&sm.ctl[kCtlNWide], 1);
-          if (w < wide_cap) sm.wide[w] = entry;
-          else sm.ctl[kCtlWideOverflow] = 1;   // ray loop falls back to sweeping every slot
         }
       }
     }
     sm.rec[2 * slot] = rec;
-    reinterpret_cast<float*>(sm.rec + 2 * slot + 1)[0] = k.c;
+    float4* r2 = sm.rec + 2 * slot + 1;
+    r2->x = k.c;
+    r2->z = __int_as_float(packed);
+    r2->w = mind2;
   }
   if (counters != nullptr) {
     for (int o = 16; o > 0; o >>= 1) n_valid += __shfl_down_sync(0xffffffffu, n_valid, o);
     if ((threadIdx.x & 31) == 0 && n_valid) atomicAdd(counters + 1, (unsigned long long)n_valid);
+  }
+}
+
+__device__ void fill_buckets(const SmemView& sm, int K, int wide_cap) {
+  const int n_cand = sm.ctl[kCtlNCand];
+  for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
+    const float4 r1 = sm.rec[2 * slot];
+    if (!(r1.x == r1.x)) continue;   // not a candidate
+    const float4 r2 = sm.rec[2 * slot + 1];
+    const int packed = __float_as_int(r2.z);
+    const float mind2 = r2.w;
+    const bool wrap = r1.x > r1.y;
+    const int inc = wrap ? 0x10000 : 1;
+    const uint16_t entry = (uint16_t)slot;
+    bool spilled = false;
+    for (int part = 0; part < 2; ++part) {
+      const int ca = part ? 0 : (packed & 1023);
+      const int cb = part ? ((packed >> 20) & 1023) - 1 : ((packed >> 10) & 1023);
+      for (int c = ca; c <= cb; ++c) {
+        if (mind2 > kOcclMargin * __uint_as_float(sm.zmax2[c])) continue;   // occluded in this chunk
+        const int old = atomicAdd(&sm.cnt[c], inc);
+        const int na = old & 0xffff, nb = old >> 16;
+        if (na + nb < K) {
+          sm.pool[c * K + (wrap ? K - 1 - nb : na)] = entry;
+        } else {
+          atomicSub(&sm.cnt[c], inc);   // bucket full: stays full from here on
+          spilled = true;
+        }
+      }
+    }
+    if (spilled) {
+      const int w = atomicAdd(&sm.ctl[kCtlNWide], 1);
+      if (w < wide_cap) sm.wide[w] = entry;
+      else sm.ctl[kCtlWideOverflow] = 1;   // ray loop falls back to sweeping every slot
+    }
   }
 }
 
@@ -546,7 +629,25 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
   const int K = bucket_capacity(c.cap, (c.max_rays + 31) >> 5, n_chunks);
   if (threadIdx.x == 0) build_rows(sm, c.src, fan, n_obj, c.max_rows);
   if (threadIdx.x >= 32 && threadIdx.x < 36) sm.ctl[threadIdx.x - 32] = 0;
-  for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) sm.cnt[k] = 0;
+  if (threadIdx.x == 64) {
+    // wedge of directions behind the fan: CCW from e1 (last ray + margin) to e2
+    // (first ray - margin); used only when it is narrower than half a turn
+    const float last = (float)(fan.num_rays - 1) * L.da;
+    const float width = k2PiF - last - 2.f * kWedgeMargin;
+    const bool on = L.cull_ok && fabsf(fan.amin) <= 8.0f && width > 1e-2f && width < kPiF - 1e-2f;
+    float* wf = reinterpret_cast<float*>(sm.ctl + kCtlWedge);
+    float s1 = 0.f, c1 = 0.f, s2 = 0.f, c2 = 0.f;
+    if (on) {
+      sincosf(fan.amin + last + kWedgeMargin, &s1, &c1);
+      sincosf(fan.amin - kWedgeMargin, &s2, &c2);
+    }
+    wf[0] = c1; wf[1] = s1; wf[2] = c2; wf[3] = s2;
+    sm.ctl[kCtlWedgeOn] = on ? 1 : 0;
+  }
+  for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) {
+    sm.cnt[k] = 0;
+    sm.zmax2[k] = 0x7f800000u;   // +inf; valid across passes (a bound from any candidate holds)
+  }
   __syncthreads();
   const int v_total = sm.row_v0[sm.ctl[kCtlNRows]];
   int pass = 0;
@@ -555,7 +656,9 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1);
     __syncthreads();
     if (pass == 0 || sm.ctl[kCtlNCand] > 0) {   // block-uniform: a later pass may be empty
-      make_records(sm, L, K, c.cap / 2, c.counters);
+      make_records(sm, L, c.counters);
+      __syncthreads();
+      fill_buckets(sm, K, c.cap / 2);
       __syncthreads();
       ray_loop(sm, fan, L, K, c.cap / 2, pass, c.multipass != 0, c.counters);
     }
