@@ -124,6 +124,11 @@ __device__ __forceinline__ bool near_a_ray(const Lattice& L, float a) {
   return d <= L.th_idx || fabsf(t - L.period) <= L.th_idx;
 }
 
+// float(atan2(double)) of vector_map.cpp:449-450; out of line (rare path, large body).
+__device__ __noinline__ float atan2_ref(float y, float x) {
+  return (float)atan2((double)y, (double)x);
+}
+
 // Per-candidate constants of the ray fill (vector_map.cpp:444-459,471,473).
 // wraps_around is not stored: after the reference's swap, a wrapping interval
 // has a0 > a1 and a plain one a0 < a1 (|a0-a1| >= 1e-4 is guaranteed), so
@@ -157,8 +162,8 @@ __device__ __forceinline__ SegCast make_cast(float p0x, float p0y, float p1x, fl
   bool exact = !L.lazy_ok || fabsf(dab - 1e-4f) <= 4e-6f || fabsf(dab - kPiF) <= 4e-6f;
   if (!exact) exact = near_a_ray(L, a0) || near_a_ray(L, a1);
   if (exact) {
-    a0 = (float)atan2((double)p0y, (double)p0x);  // :449-450 (double atan2)
-    a1 = (float)atan2((double)p1y, (double)p1x);
+    a0 = atan2_ref(p0y, p0x);  // :449-450 (double atan2)
+    a1 = atan2_ref(p1y, p1x);
   }
   if (fabs((double)(a0 - a1)) < 0.0001) return k;     // :451
   const bool wraps = fabs((double)(a1 - a0)) > kPiD;  // :452

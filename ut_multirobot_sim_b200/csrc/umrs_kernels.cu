@@ -57,7 +57,7 @@ struct SmemView {
   int32_t* row_s0;   // [max_rows] first source index of row r (object row: 0)
   int32_t* ctl;      // [16] n_cand, wide overflow, n_wide, next_chunk, n_rows, wedge flag, -, -, wedge[4]
   float4* obj;       // [n_obj_lines] world object lines (world step only)
-  float* ent;        // [n_ent][5] {x, y, theta, sin, cos} (world step only)
+  float* ent;        // [n_ent][8] {x, y, theta, sin, cos (AngleMod theta), sin, cos (theta), -} (world step only)
 };
 enum { kCtlNCand = 0, kCtlWideOverflow = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4,
        kCtlWedgeOn = 5, kCtlWedge = 8 /* 4 floats: e1x, e1y, e2x, e2y */ };
@@ -90,7 +90,7 @@ __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int ma
       sizeof(int32_t) * (size_t)(max_rows + 1),  // row_s0
       sizeof(int32_t) * 16,                    // ctl
       sizeof(float4) * (size_t)n_obj_lines,    // obj
-      sizeof(float) * 5 * (size_t)n_ent,       // ent
+      sizeof(float) * 8 * (size_t)n_ent,       // ent
       multipass ? sizeof(float) * (size_t)max_rays : 0};  // best_q
   SmemOffsets L;
   size_t o = 0;
@@ -182,6 +182,11 @@ __device__ void build_rows(const SmemView& sm, const MapSource& src, const Fan& 
   sm.row_v0[r] = v;
   sm.ctl[kCtlNRows] = r;
 }
+
+// sinf / cosf of the reference (float overloads), kept out of line: each inlined
+// copy drags a Payne-Hanek slow path along, and the step kernel's instruction
+// footprint is what its no_instruction stalls pay for.
+__device__ __noinline__ float2 sincos_ref(float a) { return make_float2(sinf(a), cosf(a)); }
 
 constexpr float kWedgeMargin = 1e-3f;   // rad; dominates every rounding in the wedge test by 1000x
 
@@ -276,7 +281,7 @@ __device__ __forceinline__ ChunkRanges chunk_ranges(int lo, int hi, const Lattic
 // the ray loop span-checks per chunk (it may then be tested twice in chunks that
 // had room -- harmless for a minimum).
 __device__ __forceinline__ int bucket_capacity(int cap, int n_chunks_max, int n_chunks) {
-  const int k = (int)(pool_entries(cap, n_chunks_max) / (size_t)n_chunks) & ~7;
+  const int k = (int)((unsigned)pool_entries(cap, n_chunks_max) / (unsigned)n_chunks) & ~7;
   return k > 248 ? 248 : k;   // >= 48 by construction of the pool
 }
 
@@ -638,8 +643,9 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     float* wf = reinterpret_cast<float*>(sm.ctl + kCtlWedge);
     float s1 = 0.f, c1 = 0.f, s2 = 0.f, c2 = 0.f;
     if (on) {
-      sincosf(fan.amin + last + kWedgeMargin, &s1, &c1);
-      sincosf(fan.amin - kWedgeMargin, &s2, &c2);
+      const float2 w1 = sincos_ref(fan.amin + last + kWedgeMargin);
+      const float2 w2 = sincos_ref(fan.amin - kWedgeMargin);
+      s1 = w1.x; c1 = w1.y; s2 = w2.x; c2 = w2.y;
     }
     wf[0] = c1; wf[1] = s1; wf[2] = c2; wf[3] = s2;
     sm.ctl[kCtlWedgeOn] = on ? 1 : 0;
@@ -766,10 +772,12 @@ __device__ void robot_step(RobotState& s, const umrs_robot_params& p, double dt,
       const float arc = dist * desired_curvature;
       dtheta = (float)((double)arc + ((double)n1 * dt) * (double)p.ak_angular_error_bias +
                        (double)((n2 * p.ak_angular_error_rate) * fabsf(arc)));
-      dx = r * sinf(dtheta);
-      dy = (float)((double)r * (1.0 - (double)cosf(dtheta)));
+      const float2 sc = sincos_ref(dtheta);
+      dx = r * sc.x;
+      dy = (float)((double)r * (1.0 - (double)sc.y));
     }
-    const float sn = sinf(s.pose[2]), cs = cosf(s.pose[2]);
+    const float2 scp = sincos_ref(s.pose[2]);
+    const float sn = scp.x, cs = scp.y;
     s.pose[0] = s.pose[0] + (cs * dx - sn * dy);
     s.pose[1] = s.pose[1] + (sn * dx + cs * dy);
     s.pose[2] = angle_mod_f(s.pose[2] + dtheta);
@@ -782,8 +790,9 @@ __device__ void robot_step(RobotState& s, const umrs_robot_params& p, double dt,
     const float dx = (float)((double)s.vel[0] * dt + (0.5 * (double)acc_times_dt) * dt);
     s.vel[0] = (float)s.linear_vel;
     s.vel[2] = (float)s.angular_vel;
-    s.pose[0] = s.pose[0] + cosf(s.pose[2]) * dx;
-    s.pose[1] = s.pose[1] + sinf(s.pose[2]) * dx;
+    const float2 scp = sincos_ref(s.pose[2]);
+    s.pose[0] = s.pose[0] + scp.y * dx;
+    s.pose[1] = s.pose[1] + scp.x * dx;
     s.pose[2] = (float)angle_mod_d((double)s.pose[2] + (double)s.vel[2] * dt);
   } else {
     // omnidirectional_model.cpp:82-123
@@ -813,7 +822,8 @@ __device__ void robot_step(RobotState& s, const umrs_robot_params& p, double dt,
     if (fabsf(desired_ang) > max_angle_accel)  // :115 quirk kept
       delta_ang = (float)signf_(delta_ang) * max_angle_accel;
     s.vel[2] = s.vel[2] + delta_ang;
-    const float sn = sinf(s.pose[2]), cs = cosf(s.pose[2]);
+    const float2 scp = sincos_ref(s.pose[2]);
+    const float sn = scp.x, cs = scp.y;
     const float rx = cs * s.vel[0] - sn * s.vel[1];
     const float ry = sn * s.vel[0] + cs * s.vel[1];
     const float dtf = (float)dt;
@@ -913,9 +923,14 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
     }
     // HumanObject::Transform rotation, human_object.cpp:132: R(AngleMod(angle))
     const float am = angle_mod_f(pth);
-    float* en = sm.ent + 5 * e;
+    float* en = sm.ent + 8 * e;
     en[0] = px; en[1] = py; en[2] = pth;
-    en[3] = sinf(am); en[4] = cosf(am);
+    const float2 sca = sincos_ref(am);
+    en[3] = sca.x; en[4] = sca.y;
+    if (e >= p.O + p.H) {   // laser pose of a robot: sin/cos of the raw angle (simulator.cpp:398-401)
+      const float2 scl = sincos_ref(pth);
+      en[5] = scl.x; en[6] = scl.y;
+    }
   }
   __syncthreads();
 
@@ -923,7 +938,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   for (int l = t; l < p.L_obj; l += blockDim.x) {
     const int e = p.line_ent[l];
     const float4 tm = __ldg(p.tmpl + l);
-    const float* en = sm.ent + 5 * e;
+    const float* en = sm.ent + 8 * e;
     const float sn = en[3], cs = en[4];
     float4 o;
     o.x = (cs * tm.x - sn * tm.y) + en[0];
@@ -936,12 +951,12 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
 
   // ---- fan of robot r (simulator.cpp:398-411) ----------------------------------
   const umrs_robot_params& me = p.robots[r];
-  const float* en = sm.ent + 5 * (p.O + p.H + r);
+  const float* en = sm.ent + 8 * (p.O + p.H + r);
   Fan fan;
   {
     // laserLoc = t + Rotation2Df(angle) * (laser_x, laser_y): sin/cos of the raw
     // pose angle (float overloads inside Eigen)
-    const float sn = sinf(en[2]), cs = cosf(en[2]);
+    const float sn = en[5], cs = en[6];
     fan.lx = en[0] + (cs * me.laser.loc_x - sn * me.laser.loc_y);
     fan.ly = en[1] + (sn * me.laser.loc_x + cs * me.laser.loc_y);
     fan.amin = me.laser.angle_min + en[2];
