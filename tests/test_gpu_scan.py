@@ -273,3 +273,82 @@ def test_bucket_overflow_paths(oracle, n_walls):
                      np.float32)
         r, i = vmap.GetPredictedScan(f[:2], 0.4, 100.0, f[2], f[3], 1081, return_index=True)
         check_against_tierb(oracle, segs, None, f, 100.0, 1081, r, i)
+
+
+def test_back_wedge_cull_keeps_every_covering_segment(oracle):
+    """The gather drops segments that lie entirely in the wedge of directions behind a
+    fan wider than half a turn.  Segments that straddle either fan edge, touch the
+    wedge margin, pass through the laser origin's neighbourhood or end exactly on
+    the edge rays must survive: tier B on hand-placed segments around both edges,
+    for several headings and fan widths (just above pi .. almost a full turn)."""
+    rng = np.random.default_rng(77)
+    for span_deg in (181.0, 200.0, 270.0, 340.0, 359.0):
+        span = np.deg2rad(span_deg)
+        for th in (0.0, 1.234, -2.9, 3.1, 6.0):
+            amin, amax = np.float32(th - span / 2), np.float32(th + span / 2)
+            n = 1081
+            da = (float(amax) - float(amin)) / n
+            edges = [float(amin), float(amin) + (n - 1) * da]
+            segs = []
+            for e in edges:
+                for d_ang in (-3e-3, -1.1e-3, -1e-3, -9e-4, -1e-6, 0.0, 1e-6, 9e-4, 1e-3, 1.1e-3, 3e-3):
+                    for r0, r1 in ((0.5, 3.0), (2.0, 2.5), (1e-3, 5.0)):
+                        a, b = e + d_ang, e + d_ang + rng.uniform(-0.4, 0.4)
+                        segs.append([r0 * np.cos(a), r0 * np.sin(a), r1 * np.cos(b), r1 * np.sin(b)])
+            # segments wholly behind the fan, and ones crossing the whole wedge
+            back = th + np.pi
+            half = (2 * np.pi - span) / 2
+            for f0, f1 in ((-0.9, 0.9), (-0.5, 0.2), (-1.2, 1.2), (-1.0, 1.0), (0.99, 1.01)):
+                a, b = back + f0 * half, back + f1 * half
+                segs.append([4 * np.cos(a), 4 * np.sin(a), 4 * np.cos(b), 4 * np.sin(b)])
+            segs = np.asarray(segs, np.float32) + np.array([3.0, -2.0, 3.0, -2.0], np.float32)
+            vmap = umrs.VectorMap(lines=segs)
+            fan = np.array([3.0, -2.0, amin, amax], np.float32)
+            r, i = vmap.GetPredictedScan(fan[:2], 0.4, 50.0, fan[2], fan[3], n, return_index=True)
+            check_against_tierb(oracle, segs, None, fan, 50.0, n, r, i)
+
+
+def test_occlusion_cull_against_grazing_and_nested_walls(oracle):
+    """Per-chunk occlusion cull: candidates farther than a wall that certainly covers
+    a whole 32-ray chunk are dropped from that chunk.  Nested boxes (everything
+    behind the inner box is culled), walls seen at grazing angles (ill-conditioned:
+    must neither occlude nor be culled), walls through the laser origin, segments
+    ending inside a chunk, and a far wall visible only through a one-ray gap."""
+    segs = []
+    for s in (1.0, 1.0005, 1.001, 2.0, 5.0, 20.0):       # nested boxes, two almost coincident
+        segs += [[-s, -s, s, -s], [s, -s, s, s], [s, s, -s, s], [-s, s, -s, -s]]
+    segs = np.asarray(segs, np.float32)
+    # open a 1-ray-wide gap in the inner boxes' +x wall: replace wall 1 (x = s) pieces
+    gap = 2e-3
+    extra = []
+    for s in (1.0, 1.0005, 1.001):
+        extra += [[s, -s, s, -gap], [s, gap, s, s]]
+    keep = np.ones(len(segs), bool)
+    keep[[1, 5, 9]] = False
+    segs = np.concatenate([segs[keep], np.asarray(extra, np.float32)])
+    # grazing walls and walls through the origin
+    graz = np.array([[0.3, 1e-4, 30.0, 2e-4], [-25.0, 0.0, 25.0, 0.0], [0.2, 0.2, 15.0, 15.0001],
+                     [1e-3, -3.0, 1.2e-3, 3.0], [0.5, 0.0, 0.9, 0.0]], np.float32)
+    segs = np.concatenate([segs, graz])
+    vmap = umrs.VectorMap(lines=segs)
+    for loc in ((0.0, 0.0), (0.013, -0.4), (0.9, 0.9), (-0.999, 0.5), (1.5, 0.0), (0.0, 1.00025)):
+        for amin, amax, n in ((-2.356, 2.356, 1081), (-np.pi, np.pi, 3601), (0.5, 7.0, 2048), (-0.05, 0.05, 64)):
+            fan = np.array([loc[0], loc[1], amin, amax], np.float32)
+            r, i = vmap.GetPredictedScan(fan[:2], 0.4, 30.0, fan[2], fan[3], n, return_index=True)
+            check_against_tierb(oracle, segs, None, fan, 30.0, n, r, i)
+
+
+def test_occlusion_cull_random_clutter_many_fans(oracle):
+    """Dense random clutter (short segments at all depths) from many poses: the
+    cull must never remove a winner; idx compared exactly (ties certified)."""
+    rng = np.random.default_rng(5)
+    c = rng.uniform(-30, 30, (1500, 2))
+    d = rng.normal(0, 1.5, (1500, 2))
+    segs = np.concatenate([c - d, c + d], 1).astype(np.float32)
+    vmap = umrs.VectorMap(lines=segs)
+    fans = np.stack([rng.uniform(-25, 25, 24), rng.uniform(-25, 25, 24), rng.uniform(-3, 3, 24),
+                     np.zeros(24)], 1).astype(np.float32)
+    fans[:, 3] = fans[:, 2] + np.float32(4.712389)
+    rb, ib = vmap.ScanBatch(fans, 40.0, 1081, return_index=True)
+    for k, f in enumerate(fans):
+        check_against_tierb(oracle, segs, None, f, 40.0, 1081, rb[k], ib[k])
