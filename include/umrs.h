@@ -272,6 +272,43 @@ int umrs_world_read_counters_ex(umrs_world* world, uint64_t out8[8]);
  * sum), reduced on the device; 4 doubles out.  Host buffer. */
 int umrs_world_stats(umrs_world* world, double* out4);
 
+/* ---- config ingestion without Lua -------------------------------
+ * Loads the flat subset of Lua used by the reference's config files (the .lua files under config/:
+ * assignments, Vector2/Vector3/DegToRad helpers, tables, require) in order into one
+ * global table -- config_reader::ConfigReader({env_config, robot_config}),
+ * simulator.cpp:106 -- and answers dotted lookups like lua_script.h:82-119
+ * ("laser_loc.x").  `root_dir` (nullable) is where require("config.sim_config") and
+ * relative file names resolve (the reference runs from its repository root).
+ * Constructs outside the subset fail the load with UMRS_ERR_UNSUPPORTED; an
+ * unreadable file is UMRS_ERR_IO; umrs_config_last_error() has file:line text. */
+typedef struct umrs_config umrs_config;
+int umrs_config_load(const char* const* files, int32_t n_files, const char* root_dir,
+                     umrs_config** out);
+int umrs_config_destroy(umrs_config* cfg);
+const char* umrs_config_last_error(void);
+int umrs_config_has(const umrs_config* cfg, const char* key); /* 1 / 0 */
+/* Typed getters (CONFIG_FLOAT/DOUBLE/INT/BOOL/STRING): UMRS_ERR_INVALID when the
+ * key is missing or of another type; *out is then left untouched. */
+int umrs_config_get_double(const umrs_config* cfg, const char* key, double* out);
+int umrs_config_get_float(const umrs_config* cfg, const char* key, float* out);
+int umrs_config_get_int(const umrs_config* cfg, const char* key, int32_t* out);
+int umrs_config_get_bool(const umrs_config* cfg, const char* key, int32_t* out);
+int umrs_config_get_string(const umrs_config* cfg, const char* key, char* buf, int32_t cap);
+/* CONFIG_STRINGLIST / CONFIG_VECTOR3FLIST (robot_types, start_poses, human_config_list:
+ * simulator.cpp:82,95-97). */
+int umrs_config_list_length(const umrs_config* cfg, const char* key, int32_t* n);
+int umrs_config_get_list_string(const umrs_config* cfg, const char* key, int32_t index,
+                                char* buf, int32_t cap);
+int umrs_config_get_list_vector3(const umrs_config* cfg, const char* key, int32_t index,
+                                 float out3[3]);
+/* The parameter PODs filled from the keys the reference reads (cited in
+ * umrs_config.cpp).  A missing key becomes 0 like the reference's CONFIG_* default
+ * and is counted in *n_missing (nullable).  footprint_enabled is left 0. */
+int umrs_config_laser_params(const umrs_config* cfg, umrs_laser_params* out, int32_t* n_missing);
+int umrs_config_robot_params(const umrs_config* cfg, const char* robot_type,
+                             umrs_robot_params* out, int32_t* n_missing);
+int umrs_config_human_params(const umrs_config* cfg, umrs_human_params* out, int32_t* n_missing);
+
 /* Philox4x32-10 as used for the noise (host restatement for tests):
  * counter {c0,c1,c2,c3}, key {k0,k1} -> 4 words. */
 void umrs_philox4x32(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);

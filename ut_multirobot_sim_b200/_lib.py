@@ -121,6 +121,21 @@ SIGNATURES = {
                                            C.POINTER(C.c_uint64)]),
     "umrs_world_read_counters_ex": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "umrs_world_stats": (C.c_int, [_P, C.POINTER(C.c_double)]),
+    "umrs_config_load": (C.c_int, [C.POINTER(C.c_char_p), C.c_int32, C.c_char_p, C.POINTER(_P)]),
+    "umrs_config_destroy": (C.c_int, [_P]),
+    "umrs_config_last_error": (C.c_char_p, []),
+    "umrs_config_has": (C.c_int, [_P, C.c_char_p]),
+    "umrs_config_get_double": (C.c_int, [_P, C.c_char_p, C.POINTER(C.c_double)]),
+    "umrs_config_get_float": (C.c_int, [_P, C.c_char_p, _F]),
+    "umrs_config_get_int": (C.c_int, [_P, C.c_char_p, _I]),
+    "umrs_config_get_bool": (C.c_int, [_P, C.c_char_p, _I]),
+    "umrs_config_get_string": (C.c_int, [_P, C.c_char_p, C.c_char_p, C.c_int32]),
+    "umrs_config_list_length": (C.c_int, [_P, C.c_char_p, _I]),
+    "umrs_config_get_list_string": (C.c_int, [_P, C.c_char_p, C.c_int32, C.c_char_p, C.c_int32]),
+    "umrs_config_get_list_vector3": (C.c_int, [_P, C.c_char_p, C.c_int32, _F]),
+    "umrs_config_laser_params": (C.c_int, [_P, C.POINTER(LaserParams), _I]),
+    "umrs_config_robot_params": (C.c_int, [_P, C.c_char_p, C.POINTER(RobotParams), _I]),
+    "umrs_config_human_params": (C.c_int, [_P, C.POINTER(HumanParams), _I]),
     "umrs_philox4x32": (None, [C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
                                C.POINTER(C.c_uint32)]),
 }

@@ -264,3 +264,91 @@ class World:
                 self._h = C.c_void_p()
         except Exception:
             pass
+
+
+class Config:
+    """Mirror of config_reader::ConfigReader (a list of Lua config files loaded into
+    one state, simulator.cpp:106) over umrs_config_*: typed dotted lookups and the
+    parameter structs the reference fills from its CONFIG_* variables."""
+
+    def __init__(self, files, root_dir=None):
+        lib = _lib.load()
+        if isinstance(files, (str, bytes)):
+            files = [files]
+        arr = (C.c_char_p * len(files))(*[f.encode() if isinstance(f, str) else f for f in files])
+        h = C.c_void_p()
+        st = lib.umrs_config_load(arr, len(files), root_dir.encode() if root_dir else None, C.byref(h))
+        if st != _lib.UMRS_OK:
+            raise _lib.UmrsError(st, "umrs_config_load: " + lib.umrs_config_last_error().decode())
+        self._h = h
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            _lib.load().umrs_config_destroy(self._h)
+            self._h = None
+
+    def has(self, key):
+        return bool(_lib.load().umrs_config_has(self._h, key.encode()))
+
+    def _get(self, fn, ctype, key):
+        out = ctype()
+        _lib.check(getattr(_lib.load(), fn)(self._h, key.encode(), C.byref(out)), "%s(%r)" % (fn, key))
+        return out.value
+
+    def get_double(self, key):
+        return self._get("umrs_config_get_double", C.c_double, key)
+
+    def get_float(self, key):
+        return self._get("umrs_config_get_float", C.c_float, key)
+
+    def get_int(self, key):
+        return self._get("umrs_config_get_int", C.c_int32, key)
+
+    def get_bool(self, key):
+        return bool(self._get("umrs_config_get_bool", C.c_int32, key))
+
+    def get_string(self, key):
+        buf = C.create_string_buffer(4096)
+        _lib.check(_lib.load().umrs_config_get_string(self._h, key.encode(), buf, 4096),
+                   "umrs_config_get_string(%r)" % key)
+        return buf.value.decode()
+
+    def list_length(self, key):
+        return self._get("umrs_config_list_length", C.c_int32, key)
+
+    def get_string_list(self, key):
+        out = []
+        for i in range(self.list_length(key)):
+            buf = C.create_string_buffer(4096)
+            _lib.check(_lib.load().umrs_config_get_list_string(self._h, key.encode(), i, buf, 4096),
+                       "umrs_config_get_list_string(%r)" % key)
+            out.append(buf.value.decode())
+        return out
+
+    def get_vector3_list(self, key):
+        n = self.list_length(key)
+        out = np.zeros((n, 3), np.float32)
+        for i in range(n):
+            _lib.check(_lib.load().umrs_config_get_list_vector3(
+                self._h, key.encode(), i, out[i].ctypes.data_as(C.POINTER(C.c_float))),
+                "umrs_config_get_list_vector3(%r)" % key)
+        return out
+
+    def robot_params(self, robot_type):
+        """(RobotParams, number of keys the files left undefined)."""
+        rp, miss = _lib.RobotParams(), C.c_int32()
+        _lib.check(_lib.load().umrs_config_robot_params(self._h, robot_type.encode(), C.byref(rp),
+                                                        C.byref(miss)), "umrs_config_robot_params")
+        return rp, miss.value
+
+    def human_params(self):
+        hp, miss = _lib.HumanParams(), C.c_int32()
+        _lib.check(_lib.load().umrs_config_human_params(self._h, C.byref(hp), C.byref(miss)),
+                   "umrs_config_human_params")
+        return hp, miss.value
+
+    def laser_params(self):
+        lp, miss = _lib.LaserParams(), C.c_int32()
+        _lib.check(_lib.load().umrs_config_laser_params(self._h, C.byref(lp), C.byref(miss)),
+                   "umrs_config_laser_params")
+        return lp, miss.value
