@@ -155,6 +155,13 @@ int umrs_map_get_segments(const umrs_map* map, float* segs_xyxy, int32_t cap);
  * *n_out receives the cleaned count (UMRS_ERR_INVALID if cap is too small). */
 int umrs_map_cleanup(const float* segs_xyxy, int32_t n, float* out_xyxy,
                      int32_t cap, int32_t* n_out);
+/* The same, choosing how the "first already-accepted line that crosses" search
+ * (vector_map.cpp:377-385) is done: 0 auto, 1 the reference's quadratic loop,
+ * 2 a uniform grid over the accepted lines' bounding boxes.  Every choice returns
+ * the same segments in the same order, bit for bit (tests/test_oracle.py); the
+ * grid turns the O(L^2) map load into ~O(L) for large maps. */
+int umrs_map_cleanup_ex(const float* segs_xyxy, int32_t n, float* out_xyxy, int32_t cap,
+                        int32_t* n_out, int32_t algorithm);
 
 /* ---- drop-in scan -------------------------------------------------------------
  * Same seven arguments as VectorMap::GetPredictedScan (vector_map.h:66-72) plus

@@ -291,3 +291,98 @@ def test_box_muller_distribution(oracle):
     assert abs(g.mean()) < 0.02 and abs(g.std() - 1.0) < 0.02
     from scipy import stats
     assert stats.kstest(g, "norm").pvalue > 1e-3
+
+
+def _crossing_maps():
+    """Raw maps that make Cleanup work: random clutter with thousands of crossings,
+    an axis-aligned lattice (T-junctions, shared end points, collinear overlaps,
+    duplicates), long diagonals across everything, and mixed coordinate scales."""
+    rng = np.random.default_rng(17)
+    c = rng.uniform(-40, 40, (1500, 2))
+    d = rng.normal(0, 3.0, (1500, 2))
+    clutter = np.concatenate([c - d, c + d], 1).astype(np.float32)
+    lat = []
+    for k in range(25):
+        lat += [[0, k, 24, k], [k, 0, k, 24]]            # crossings at integer points
+    lat += [[2, 3, 9, 3], [2, 3, 9, 3], [5, 3, 14, 3]]    # duplicate + collinear overlap
+    lat += [[-5, -5, 30, 30], [-5, 30, 30, -5], [0.5, 0.5, 0.5, 0.52]]   # diagonals, a < 5 cm stub
+    lattice = np.asarray(lat, np.float32)
+    # (coordinates stay below ~500 m: beyond that the 1e-4 shrink is smaller than a float
+    # ulp and the reference's own loop re-splits the same piece forever)
+    mixed = np.concatenate([clutter[:400] * 0.01, clutter[400:800] * 5.0, lattice * 3.0 + 100.0])
+    return {"clutter": clutter, "lattice": lattice, "mixed": mixed.astype(np.float32)}
+
+
+def test_grid_cleanup_equals_quadratic_and_reference(ref):
+    """the grid-accelerated Cleanup returns the reference's segments in the
+    reference's order, bit for bit -- against the product's quadratic restatement and
+    against the compiled reference's own Cleanup (oracle/_ref) on crossing-heavy maps."""
+    import ut_multirobot_sim_b200 as umrs
+    for name, raw in _crossing_maps().items():
+        q = umrs.map_cleanup(raw, algorithm=1)
+        g = umrs.map_cleanup(raw, algorithm=2)
+        a = umrs.map_cleanup(raw, algorithm=0)
+        assert len(q) > len(raw) or name == "mixed", name      # splits happened
+        assert np.array_equal(q.view(np.uint32), g.view(np.uint32)), name
+        assert np.array_equal(q.view(np.uint32), a.view(np.uint32)), name
+        if ref is not None:
+            r = ref.map_from_segments(raw, True).lines
+            assert np.array_equal(np.asarray(r, np.float32).view(np.uint32), g.view(np.uint32)), name
+
+
+def test_grid_cleanup_degenerate_inputs():
+    import ut_multirobot_sim_b200 as umrs
+    assert len(umrs.map_cleanup(np.zeros((0, 4), np.float32), algorithm=2)) == 0
+    one = np.array([[1, 1, 2, 2]], np.float32)
+    assert np.array_equal(umrs.map_cleanup(one, 2).view(np.uint32), umrs.map_cleanup(one, 1).view(np.uint32))
+    # all segments identical points / zero extent: dropped by the 5 cm rule
+    assert len(umrs.map_cleanup(np.ones((10, 4), np.float32), 2)) == 0
+    # non-finite coordinates: the grid is not used (same output as the quadratic loop);
+    # no crossing with the finite segment so the reference's loop terminates
+    bad = np.array([[0, 0, 1, 0], [np.inf, 5, np.inf, 6]], np.float32)
+    with np.errstate(invalid="ignore"):
+        assert np.array_equal(umrs.map_cleanup(bad, 2).view(np.uint32), umrs.map_cleanup(bad, 1).view(np.uint32))
+
+
+def test_grid_cleanup_large_map_fast_and_identical_on_a_sample():
+    """100k-segment city-block map + 500 long streets crossing it (config 4's segment count,
+    coordinates within +-450 m so the reference's own loop terminates): the grid finishes in
+    seconds; on a crop of a few thousand segments the quadratic loop gives the same bits.
+    Config 4's own 2 km map has no crossings, so it goes through either search unchanged."""
+    import time
+    import ut_multirobot_sim_b200 as umrs
+    from ut_multirobot_sim_b200 import synth
+    E = 900.0
+    blocks = synth.cityblock_segments(100000, extent=E, seed=99) - np.float32(E / 2)
+    # streets cross the blocks' axis-aligned walls at 20..70 degrees: at grazing angles the
+    # 1e-4 m cut leaves the piece within one float ulp of the wall it was cut at and the
+    # reference's loop (and this one, until its queue cap) re-splits it forever
+    rng = np.random.default_rng(3)
+    c = rng.uniform(-E / 2, E / 2, (500, 2))
+    ang = rng.uniform(0.35, 1.2, 500) * rng.choice([-1.0, 1.0], 500)
+    half = rng.uniform(50, 200, 500)[:, None] * np.stack([np.cos(ang), np.sin(ang)], 1)
+    streets = np.concatenate([c - half, c + half], 1).astype(np.float32)
+    raw = np.concatenate([blocks, streets])
+    t0 = time.perf_counter()
+    g = umrs.map_cleanup(raw, algorithm=2)
+    dt = time.perf_counter() - t0
+    assert len(g) > len(raw) and dt < 60.0, (len(g), dt)
+    crop = raw[(np.abs(raw[:, 0]) < 60) & (np.abs(raw[:, 1]) < 60)]
+    q = umrs.map_cleanup(crop, 1)
+    assert len(q) > len(crop)
+    assert np.array_equal(q.view(np.uint32), umrs.map_cleanup(crop, 2).view(np.uint32))
+    # config 4's map (2 km, nothing crosses): identical through both searches on a sample
+    c4 = synth.cityblock_segments(4000, extent=2000.0, seed=99)
+    assert np.array_equal(umrs.map_cleanup(c4, 1).view(np.uint32), umrs.map_cleanup(c4, 2).view(np.uint32))
+
+
+def test_cleanup_reports_inputs_the_reference_never_finishes():
+    """Beyond ~1 km the 1e-4 m cut is below the float spacing: the piece pushed back equals
+    the line that was cut and the reference's loop (vector_map.cpp:371-392) spins forever.
+    Both searches here detect the cycle and return an error instead."""
+    import ut_multirobot_sim_b200 as umrs
+    from ut_multirobot_sim_b200 import _lib
+    far = np.array([[5000, 4990, 5000, 5010], [4990, 5000, 5010, 5000]], np.float32)
+    for alg in (1, 2):
+        with pytest.raises(_lib.UmrsError):
+            umrs.map_cleanup(far, algorithm=alg)

@@ -59,15 +59,16 @@ def laser_num_rays(laser):
     return int(_lib.load().umrs_laser_num_rays(C.byref(laser)))
 
 
-def map_cleanup(segs):
-    """VectorMap::Cleanup (vector_map.cpp:367-395) on raw segments, host-side."""
+def map_cleanup(segs, algorithm=0):
+    """VectorMap::Cleanup (vector_map.cpp:367-395) on raw segments, host-side.
+    algorithm: 0 auto, 1 the reference's quadratic search, 2 uniform grid (same output)."""
     lib = _lib.load()
     segs = _segs(segs)
     cap = 4 * len(segs) + 16
     while True:
         out = np.empty((cap, 4), np.float32)
         n = C.c_int32(0)
-        st = lib.umrs_map_cleanup(_fp(segs), len(segs), _fp(out), cap, C.byref(n))
+        st = lib.umrs_map_cleanup_ex(_fp(segs), len(segs), _fp(out), cap, C.byref(n), algorithm)
         if st == _lib.UMRS_OK:
             return out[: n.value].copy()
         if n.value > cap:

@@ -292,7 +292,7 @@ int umrs_map_load_file(const char* path, umrs_map** out) {
   *out = NULL;
   std::vector<float> raw, clean;
   if (!LoadMapFile(path, &raw)) return UMRS_ERR_IO;  // the reference exit(1)s here
-  CleanupSegments(raw.data(), (int)(raw.size() / 4), &clean);
+  if (!CleanupSegments(raw.data(), (int)(raw.size() / 4), &clean)) return UMRS_ERR_UNSUPPORTED;
   return map_from_clean(clean.data(), (int32_t)(clean.size() / 4), out);
 }
 

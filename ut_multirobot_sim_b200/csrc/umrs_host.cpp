@@ -2,6 +2,7 @@
 // config files, the one-time map preparation (VectorMap::Load/Cleanup), and
 // small utilities.  No CUDA here.  Citations: file:line in the reference tree.
 #include <math.h>
+#include <cmath>
 #include <stdio.h>
 #include <string.h>
 
@@ -64,14 +65,165 @@ float Length(const Seg& l) {  // line2d.h:54-56
 }
 }  // namespace
 
-void CleanupSegments(const float* in_xyxy, int n, std::vector<float>* out_xyxy) {
+// Same result as the quadratic loop below, found through a uniform grid over the
+// kept segments' bounding boxes (Cleanup is O(L^2) and dominates map
+// loading from ~20k segments up).  What must be reproduced is "the FIRST kept line, in
+// insertion order, that Intersection() accepts" (vector_map.cpp:377-385).
+// Intersection()'s broad phase rejects pairs whose bounding boxes do not overlap with
+// exact float comparisons (line2d.h:143-146), so only kept lines whose box overlaps
+// l1's can be accepted; two overlapping boxes always share a grid cell because the cell
+// index is a monotone function of the coordinate.  Candidates are therefore the kept
+// lines registered in the cells l1's box touches (plus the few that span too many
+// cells), and the lowest kept index among the accepted ones is the reference's choice.
+namespace {
+// The reference's loop does not terminate on some inputs: where the 1e-4 m cut
+// around a crossing is below the float spacing of the coordinates (beyond ~1 km) the
+// pieces pushed back equal the line that was split, forever.  The queue is capped (far
+// above anything a terminating run reaches) and the call fails instead of hanging.
+// A piece equal to the line it was cut from meets the same kept lines again: a certain cycle.
+inline bool SameSeg(const Seg& a, const Seg& b) {
+  return a.x0 == b.x0 && a.y0 == b.y0 && a.x1 == b.x1 && a.y1 == b.y1;
+}
+inline size_t CleanupQueueLimit(int n) { return (size_t)256 * (size_t)(n > 0 ? n : 0) + 65536; }
+
+struct CleanupGrid {
+  float x0, y0, inv;
+  int gx, gy;
+  std::vector<std::vector<int>> cells;
+  std::vector<int> wide;          // kept lines spanning more than kMaxSpan cells
+  std::vector<unsigned> stamp;    // per kept line: last query that tested it
+  unsigned query = 0;
+  static constexpr int kMaxSpan = 256;
+
+  int Cx(float x) const {
+    const float f = (x - x0) * inv;
+    if (!(f > 0.f)) return 0;
+    return f >= (float)gx ? gx - 1 : (int)f;
+  }
+  int Cy(float y) const {
+    const float f = (y - y0) * inv;
+    if (!(f > 0.f)) return 0;
+    return f >= (float)gy ? gy - 1 : (int)f;
+  }
+  void Box(const Seg& s, int* cx0, int* cx1, int* cy0, int* cy1) const {
+    *cx0 = Cx(Min(s.x0, s.x1)); *cx1 = Cx(Max(s.x0, s.x1));
+    *cy0 = Cy(Min(s.y0, s.y1)); *cy1 = Cy(Max(s.y0, s.y1));
+  }
+  void Insert(const Seg& s, int kept_index) {
+    int cx0, cx1, cy0, cy1;
+    Box(s, &cx0, &cx1, &cy0, &cy1);
+    stamp.push_back(0u);
+    if ((long)(cx1 - cx0 + 1) * (cy1 - cy0 + 1) > kMaxSpan) {
+      wide.push_back(kept_index);
+      return;
+    }
+    for (int cy = cy0; cy <= cy1; ++cy)
+      for (int cx = cx0; cx <= cx1; ++cx) cells[(size_t)cy * gx + cx].push_back(kept_index);
+  }
+};
+
+bool AllFinite(const float* v, size_t n) {
+  for (size_t i = 0; i < n; ++i)
+    if (!std::isfinite(v[i])) return false;
+  return true;
+}
+}  // namespace
+
+bool CleanupSegmentsGrid(const float* in_xyxy, int n, std::vector<float>* out_xyxy) {
+  const float kShrinkDistance = 1e-4f;
+  const float kMinLineLength = 0.05f;
+  std::vector<Seg> lines(n);
+  if (n > 0) memcpy(lines.data(), in_xyxy, sizeof(Seg) * (size_t)n);
+  CleanupGrid g;
+  float xmin = 0.f, xmax = 0.f, ymin = 0.f, ymax = 0.f;
+  for (int i = 0; i < n; ++i) {
+    const Seg& s = lines[i];
+    if (i == 0) { xmin = xmax = s.x0; ymin = ymax = s.y0; }
+    xmin = Min(xmin, Min(s.x0, s.x1)); xmax = Max(xmax, Max(s.x0, s.x1));
+    ymin = Min(ymin, Min(s.y0, s.y1)); ymax = Max(ymax, Max(s.y0, s.y1));
+  }
+  const float ext = Max(Max(xmax - xmin, ymax - ymin), 1e-3f);
+  int side = (int)(sqrt((double)(n > 0 ? n : 1)) * 0.75) + 1;
+  if (side > 4096) side = 4096;
+  const float cell = ext / (float)side;
+  g.x0 = xmin; g.y0 = ymin; g.inv = 1.0f / cell;
+  g.gx = (int)((xmax - xmin) * g.inv) + 1;
+  g.gy = (int)((ymax - ymin) * g.inv) + 1;
+  g.cells.resize((size_t)g.gx * g.gy);
+  std::vector<Seg> kept;
+  kept.reserve(n);
+  const size_t limit = CleanupQueueLimit(n);
+  for (size_t i = 0; i < lines.size(); ++i) {  // the list grows while iterating
+    if (lines.size() > limit) return false;
+    const Seg l1 = lines[i];
+    if (Length(l1) < kMinLineLength) continue;
+    int best = -1;
+    float bpx = 0.f, bpy = 0.f;
+    ++g.query;
+    auto consider = [&](int k) {
+      if (g.stamp[(size_t)k] == g.query) return;
+      g.stamp[(size_t)k] = g.query;
+      if (best >= 0 && k > best) return;
+      float px, py;
+      if (Intersection(kept[(size_t)k], l1, &px, &py)) { best = k; bpx = px; bpy = py; }
+    };
+    int cx0, cx1, cy0, cy1;
+    g.Box(l1, &cx0, &cx1, &cy0, &cy1);
+    for (int cy = cy0; cy <= cy1; ++cy)
+      for (int cx = cx0; cx <= cx1; ++cx)
+        for (int k : g.cells[(size_t)cy * g.gx + cx]) consider(k);
+    for (int k : g.wide) consider(k);
+    if (best >= 0) {
+      float dx, dy;
+      Dir(l1, &dx, &dy);
+      const float sx = kShrinkDistance * dx, sy = kShrinkDistance * dy;
+      lines.push_back(Seg{l1.x0, l1.y0, bpx - sx, bpy - sy});
+      lines.push_back(Seg{bpx + sx, bpy + sy, l1.x1, l1.y1});
+      if (SameSeg(lines[lines.size() - 2], l1) || SameSeg(lines.back(), l1)) return false;
+    } else {
+      g.Insert(l1, (int)kept.size());
+      kept.push_back(l1);
+    }
+  }
+  for (Seg& l : kept) {  // ShrinkLine, vector_map.cpp:359-365
+    const float len = Length(l);
+    float dx, dy;
+    Dir(l, &dx, &dy);
+    if ((double)len < 2.0 * (double)kShrinkDistance) continue;
+    l.x0 = l.x0 + kShrinkDistance * dx;
+    l.y0 = l.y0 + kShrinkDistance * dy;
+    l.x1 = l.x1 - kShrinkDistance * dx;
+    l.y1 = l.y1 - kShrinkDistance * dy;
+  }
+  out_xyxy->resize(kept.size() * 4);
+  if (!kept.empty()) memcpy(out_xyxy->data(), kept.data(), sizeof(Seg) * kept.size());
+  return true;
+}
+
+// algorithm: 0 auto (grid from 512 segments up, if every coordinate is finite),
+// 1 the reference's quadratic loop, 2 grid.
+bool CleanupSegmentsWith(const float* in_xyxy, int n, int algorithm, std::vector<float>* out_xyxy) {
+  const bool finite = AllFinite(in_xyxy, (size_t)(n > 0 ? n : 0) * 4);
+  if (algorithm == 2 ? finite : (algorithm == 0 && n >= 512 && finite)) {
+    return CleanupSegmentsGrid(in_xyxy, n, out_xyxy);
+  }
+  return CleanupSegmentsQuadratic(in_xyxy, n, out_xyxy);
+}
+
+bool CleanupSegments(const float* in_xyxy, int n, std::vector<float>* out_xyxy) {
+  return CleanupSegmentsWith(in_xyxy, n, 0, out_xyxy);
+}
+
+bool CleanupSegmentsQuadratic(const float* in_xyxy, int n, std::vector<float>* out_xyxy) {
   const float kShrinkDistance = 1e-4f;
   const float kMinLineLength = 0.05f;
   std::vector<Seg> lines(n);
   if (n > 0) memcpy(lines.data(), in_xyxy, sizeof(Seg) * (size_t)n);
   std::vector<Seg> kept;
   kept.reserve(n);
+  const size_t limit = CleanupQueueLimit(n);
   for (size_t i = 0; i < lines.size(); ++i) {  // the list grows while iterating
+    if (lines.size() > limit) return false;
     const Seg l1 = lines[i];
     if (Length(l1) < kMinLineLength) continue;
     bool split = false;
@@ -83,6 +235,7 @@ void CleanupSegments(const float* in_xyxy, int n, std::vector<float>* out_xyxy) 
         const float sx = kShrinkDistance * dx, sy = kShrinkDistance * dy;
         lines.push_back(Seg{l1.x0, l1.y0, px - sx, py - sy});
         lines.push_back(Seg{px + sx, py + sy, l1.x1, l1.y1});
+        if (SameSeg(lines[lines.size() - 2], l1) || SameSeg(lines.back(), l1)) return false;
         split = true;
         break;
       }
@@ -101,6 +254,7 @@ void CleanupSegments(const float* in_xyxy, int n, std::vector<float>* out_xyxy) 
   }
   out_xyxy->resize(kept.size() * 4);
   if (!kept.empty()) memcpy(out_xyxy->data(), kept.data(), sizeof(Seg) * kept.size());
+  return true;
 }
 
 // VectorMap::Load, vector_map.cpp:397-411: "%f,%f,%f,%f" until the first mismatch.
@@ -291,9 +445,17 @@ void umrs_default_human(umrs_human_params* o) {
 
 int umrs_map_cleanup(const float* segs_xyxy, int32_t n, float* out_xyxy, int32_t cap,
                      int32_t* n_out) {
-  if (n < 0 || (n > 0 && segs_xyxy == NULL) || n_out == NULL) return UMRS_ERR_INVALID;
+  return umrs_map_cleanup_ex(segs_xyxy, n, out_xyxy, cap, n_out, 0);
+}
+
+int umrs_map_cleanup_ex(const float* segs_xyxy, int32_t n, float* out_xyxy, int32_t cap,
+                        int32_t* n_out, int32_t algorithm) {
+  if (n < 0 || (n > 0 && segs_xyxy == NULL) || n_out == NULL || algorithm < 0 || algorithm > 2)
+    return UMRS_ERR_INVALID;
   std::vector<float> out;
-  umrs::CleanupSegments(segs_xyxy, n, &out);
+  *n_out = 0;
+  // the split queue ran away: an input on which the reference's own loop never ends
+  if (!umrs::CleanupSegmentsWith(segs_xyxy, n, algorithm, &out)) return UMRS_ERR_UNSUPPORTED;
   *n_out = (int32_t)(out.size() / 4);
   if (*n_out > cap || (out_xyxy == NULL && *n_out > 0)) return UMRS_ERR_INVALID;
   if (!out.empty()) memcpy(out_xyxy, out.data(), sizeof(float) * out.size());

@@ -4,8 +4,13 @@
 #include "../../include/umrs.h"
 
 namespace umrs {
-// VectorMap::Cleanup + ShrinkLine (vector_map.cpp:359-395).
-void CleanupSegments(const float* in_xyxy, int n, std::vector<float>* out_xyxy);
+// VectorMap::Cleanup + ShrinkLine (vector_map.cpp:359-395).  false: the split queue ran away
+// (inputs on which the reference's own loop never ends).
+bool CleanupSegments(const float* in_xyxy, int n, std::vector<float>* out_xyxy);
+// The same output by the reference's quadratic loop / through a uniform grid / chosen by size.
+bool CleanupSegmentsQuadratic(const float* in_xyxy, int n, std::vector<float>* out_xyxy);
+bool CleanupSegmentsGrid(const float* in_xyxy, int n, std::vector<float>* out_xyxy);
+bool CleanupSegmentsWith(const float* in_xyxy, int n, int algorithm, std::vector<float>* out_xyxy);
 // VectorMap::Load's parse loop (vector_map.cpp:404-407); false if unreadable.
 bool LoadMapFile(const char* path, std::vector<float>* raw_xyxy);
 // Footprint templates at pose (0,0,0) (entity_base.h:37-38).
