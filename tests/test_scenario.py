@@ -139,6 +139,9 @@ def test_scenario_batch_steps_on_the_gpu_like_the_oracle(oracle, tmp_path):
             row.append((s, hp))
         hstates.append(row)
     n = umrs.laser_num_rays(car.laser)
+    # object lines of a world: [humans][robot bodies]; a scan does not see its own body
+    assert world.object_lines_per_world == 20 * H + (4 if car.footprint_enabled else 0)
+    own = (20 * H, world.object_lines_per_world)
     seen_humans = 0
     rng = np.random.default_rng(0)
     for step in range(60):
@@ -156,8 +159,8 @@ def test_scenario_batch_steps_on_the_gpu_like_the_oracle(oracle, tmp_path):
             lines, fans = world.GetLines(), world.fan_params()
             for w in range(W):
                 check_against_tierb(oracle, segs, lines[w], fans[w, 0], car.laser.range_max, n,
-                                    ranges[w], idx[w])
-                seen_humans += int((idx[w] >= len(segs)).sum())
+                                    ranges[w], idx[w], skip=own)
+                seen_humans += int(((idx[w] >= len(segs)) & (idx[w] < len(segs) + 20 * H)).sum())
     assert seen_humans > 100       # the humans do occlude the scans
     # 60 steps at 1 m/s = 1.5 m: everybody moved, nobody reached a 20 m goal yet
     assert np.all(np.linalg.norm(ghp[..., :2] - batch.human_start[..., :2], axis=-1) > 1.0)

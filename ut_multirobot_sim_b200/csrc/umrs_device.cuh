@@ -151,20 +151,47 @@ struct SegCast {
 // from their thresholds) the cheap angles are stored -- every decision, hence
 // every output bit, is the same.  Otherwise the double atan2 is evaluated.
 // The range itself never depends on a0/a1 beyond the swap decision.
-__device__ __forceinline__ SegCast make_cast(float p0x, float p0y, float p1x, float p1y,
-                                             const Lattice& L) {
+//
+// Each endpoint is decided on its own: a threshold comparison within 4e-6 of
+// its threshold makes BOTH exact; otherwise only an endpoint with a ray within
+// kAngleSlack of it needs the exact value (the thresholds keep their margin when
+// one angle moves by <= 6e-7, and the ray comparisons of the two endpoints are
+// independent).
+struct CastAngles {
+  float a0, a1;        // atan2f values
+  bool need0, need1;   // the reference's float(atan2(double)) must replace them
+};
+
+__device__ __forceinline__ CastAngles cast_angles(float p0x, float p0y, float p1x, float p1y,
+                                                  const Lattice& L) {
+  CastAngles r;
+  r.a0 = atan2f(p0y, p0x);
+  r.a1 = atan2f(p1y, p1x);
+  const float dab = fabsf(r.a0 - r.a1);
+  const bool both = !L.lazy_ok || fabsf(dab - 1e-4f) <= 4e-6f || fabsf(dab - kPiF) <= 4e-6f;
+  r.need0 = both || near_a_ray(L, r.a0);
+  r.need1 = both || near_a_ray(L, r.a1);
+  return r;
+}
+
+// Replaces the flagged angles by float(atan2(double)): one call site, executed a
+// second time only by lanes that need both (a diverged warp pays per call).
+__device__ __forceinline__ void exact_angles(CastAngles& r, float p0x, float p0y, float p1x,
+                                             float p1y) {
+  for (int it = 0; it < 2; ++it) {
+    if (!(r.need0 || r.need1)) break;
+    const bool first = r.need0;
+    const float v = atan2_ref(first ? p0y : p1y, first ? p0x : p1x);  // :449-450 (double atan2)
+    if (first) { r.a0 = v; r.need0 = false; } else { r.a1 = v; r.need1 = false; }
+  }
+}
+
+// vector_map.cpp:451-459,471,473 on settled angles.
+__device__ __forceinline__ SegCast finish_cast(float a0, float a1, float p0x, float p0y, float p1x,
+                                               float p1y) {
   SegCast k;
   k.valid = false;
   k.a0 = 0.f; k.a1 = 0.f; k.nx = 0.f; k.ny = 0.f; k.c = 0.f; k.arc = 0.f;
-  float a0 = atan2f(p0y, p0x);
-  float a1 = atan2f(p1y, p1x);
-  const float dab = fabsf(a0 - a1);
-  bool exact = !L.lazy_ok || fabsf(dab - 1e-4f) <= 4e-6f || fabsf(dab - kPiF) <= 4e-6f;
-  if (!exact) exact = near_a_ray(L, a0) || near_a_ray(L, a1);
-  if (exact) {
-    a0 = atan2_ref(p0y, p0x);  // :449-450 (double atan2)
-    a1 = atan2_ref(p1y, p1x);
-  }
   if (fabs((double)(a0 - a1)) < 0.0001) return k;     // :451
   const bool wraps = fabs((double)(a1 - a0)) > kPiD;  // :452
   if ((wraps && a0 < a1) || (!wraps && a0 > a1)) {    // :453-457
@@ -189,6 +216,13 @@ __device__ __forceinline__ SegCast make_cast(float p0x, float p0y, float p1x, fl
   k.valid = true;
   k.arc = wraps ? (a1 + k2PiF) - a0 : a1 - a0;
   return k;
+}
+
+__device__ __forceinline__ SegCast make_cast(float p0x, float p0y, float p1x, float p1y,
+                                             const Lattice& L) {
+  CastAngles r = cast_angles(p0x, p0y, p1x, p1y, L);
+  exact_angles(r, p0x, p0y, p1x, p1y);
+  return finish_cast(r.a0, r.a1, p0x, p0y, p1x, p1y);
 }
 
 // vector_map.cpp:469-470, inclusive at both ends.
