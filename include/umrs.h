@@ -274,6 +274,10 @@ int umrs_world_read_counters(umrs_world* world, uint64_t* ray_seg_tests,
  * chunk_seg_pairs, passes (summed over fans), tie sweeps, spilled-candidate
  * list entries, fans that swept every slot, spare}. */
 int umrs_world_read_counters_ex(umrs_world* world, uint64_t out8[8]);
+/* Development builds only (-DUMRS_PHASE_TIMING): clock cycles of every fan CTA's critical
+ * path per phase, summed over the fans of the last step: {world phase A, setup, gather,
+ * records, buckets, ray loop, finalise, spare}.  All zero in the shipped build. */
+int umrs_world_read_phase_cycles(umrs_world* world, uint64_t out8[8]);
 
 /* K3: per-shard statistics of the last step's ranges (count of hits, min, max,
  * sum), reduced on the device; 4 doubles out.  Host buffer. */

@@ -121,6 +121,7 @@ SIGNATURES = {
     "umrs_world_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                            C.POINTER(C.c_uint64)]),
     "umrs_world_read_counters_ex": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
+    "umrs_world_read_phase_cycles": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "umrs_world_stats": (C.c_int, [_P, C.POINTER(C.c_double)]),
     "umrs_config_load": (C.c_int, [C.POINTER(C.c_char_p), C.c_int32, C.c_char_p, C.POINTER(_P)]),
     "umrs_config_destroy": (C.c_int, [_P]),

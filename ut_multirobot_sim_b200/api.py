@@ -253,6 +253,13 @@ class World:
         return {"ray_seg_tests": a.value, "segs_prepared": b.value, "chunk_seg_pairs": c.value,
                 "passes": ex[3], "tie_sweeps": ex[4], "spilled_entries": ex[5], "sweep_all_fans": ex[6]}
 
+    def phase_cycles(self):
+        """Dev builds (-DUMRS_PHASE_TIMING): summed critical-path cycles per phase; zeros otherwise."""
+        ex = (C.c_uint64 * 8)()
+        check(self._lib.umrs_world_read_phase_cycles(self._h, ex), "read_phase_cycles")
+        names = ("phase_a", "setup", "gather", "records", "buckets", "ray_loop", "finalise")
+        return {k: int(ex[i]) for i, k in enumerate(names)}
+
     def stats(self):
         out = (C.c_double * 4)()
         check(self._lib.umrs_world_stats(self._h, out), "umrs_world_stats")

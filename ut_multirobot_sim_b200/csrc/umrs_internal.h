@@ -63,11 +63,14 @@ struct MapSource {
   int32_t n_map_total;        // object line o gets hit index n_map_total + o
 };
 
+constexpr int kNumCounters = 16;
+
 struct ScanCommon {
   MapSource src;
   float* ranges;                 // [fans][num_rays] or [W][rays_per_world]
   int32_t* hit_idx;              // nullable, same shape
-  unsigned long long* counters;  // nullable: {tests, segs_prepared, chunk_seg_pairs, passes}
+  unsigned long long* counters;  // nullable: [kNumCounters] {tests, segs_prepared, chunk_seg_pairs, passes,
+                                 // tie sweeps, spilled, sweep-all fans, -, 8 phase-cycle sums (dev builds)}
   int32_t cap;                   // candidate slots per pass (smem sizing)
   int32_t max_rows;              // source rows a fan can touch (smem sizing)
   int32_t max_rays;              // largest num_rays of any fan of the launch (smem sizing)

@@ -39,6 +39,24 @@
 #define UMRS_MIN_CTAS 4   // resident fan CTAs per SM the register budget is held to (64 regs)
 #endif
 
+// Dev build (-DUMRS_PHASE_TIMING): thread 0 of every fan CTA adds the clock64 cycles between
+// phase boundaries to counters[8 + k] (k: 0 world phase A, 1 setup, 2 gather, 3 records,
+// 4 buckets, 5 ray loop, 6 finalise) -- where a CTA's critical path goes.  Off: nothing.
+#ifdef UMRS_PHASE_TIMING
+#define UMRS_STAMP(ctrs, k)                                                        \
+  do {                                                                             \
+    if (threadIdx.x == 0 && (ctrs) != nullptr) {                                   \
+      const long long n_ = clock64();                                              \
+      atomicAdd((ctrs) + 8 + (k), (unsigned long long)(n_ - umrs_tlast));          \
+      umrs_tlast = n_;                                                             \
+    }                                                                              \
+  } while (0)
+#define UMRS_STAMP_INIT long long umrs_tlast = clock64()
+#else
+#define UMRS_STAMP(ctrs, k) do { } while (0)
+#define UMRS_STAMP_INIT do { } while (0)
+#endif
+
 namespace umrs {
 
 // ---- shared-memory carve-up --------------------------------------------------
@@ -629,6 +647,7 @@ __device__ void finalise(const SmemView& sm, const Fan& fan, float* __restrict__
 __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan,
                          const float4* obj_segs, int n_obj, int skip_lo, int skip_hi,
                          float* ranges, int32_t* hit_idx, const PostProcess& post) {
+  UMRS_STAMP_INIT;
   const Lattice L = make_lattice(fan.amin, fan.amax, fan.num_rays);
   const int n_chunks = (fan.num_rays + 31) >> 5;
   const int K = bucket_capacity(c.cap, (c.max_rays + 31) >> 5, n_chunks);
@@ -655,20 +674,25 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     sm.zmax2[k] = 0x7f800000u;   // +inf; valid across passes (a bound from any candidate holds)
   }
   __syncthreads();
+  UMRS_STAMP(c.counters, 1);
   const int v_total = sm.row_v0[sm.ctl[kCtlNRows]];
   int pass = 0;
   for (int v0 = 0; v0 < v_total || pass == 0; v0 += c.cap, ++pass) {
     const int v1 = v0 + c.cap < v_total ? v0 + c.cap : v_total;
     gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1);
     __syncthreads();
+    UMRS_STAMP(c.counters, 2);
     if (pass == 0 || sm.ctl[kCtlNCand] > 0) {   // block-uniform: a later pass may be empty
       make_records(sm, L, c.counters);
       __syncthreads();
+      UMRS_STAMP(c.counters, 3);
       fill_buckets(sm, K, c.cap / 2);
       __syncthreads();
+      UMRS_STAMP(c.counters, 4);
       ray_loop(sm, fan, L, K, c.cap / 2, pass, c.multipass != 0, c.counters);
     }
     __syncthreads();
+    UMRS_STAMP(c.counters, 5);
     if (v0 + c.cap < v_total) {   // another pass: reset the per-pass state
       if (threadIdx.x < 4) sm.ctl[threadIdx.x] = 0;
       for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) sm.cnt[k] = 0;
@@ -677,6 +701,10 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
   }
   if (c.counters != nullptr && threadIdx.x == 0) atomicAdd(c.counters + 3, (unsigned long long)pass);
   finalise(sm, fan, ranges, hit_idx, post);
+#ifdef UMRS_PHASE_TIMING
+  __syncthreads();
+  UMRS_STAMP(c.counters, 6);
+#endif
 }
 
 // ---- scan-only kernel (umrs_predicted_scan / umrs_scan_batch) -------------------
@@ -879,6 +907,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   const bool owner = (r == 0);
   const double dt = (double)p.dt;  // `const double& dt` bound to float CONFIG_DT
   const int t = threadIdx.x;
+  UMRS_STAMP_INIT;
 
   // ---- phase A: entity steps -> sm.ent[e] = {x, y, theta, sin, cos} ----------
   for (int e = t; e < n_ent; e += blockDim.x) {
@@ -976,6 +1005,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   post.step_lo = p.step_lo; post.step_hi = p.step_hi;
   post.fan_global = (uint32_t)(p.world_base + w) * (uint32_t)p.R + (uint32_t)r;
   const size_t off = (size_t)w * (size_t)p.rays_per_world + (size_t)p.ray_off[r];
+  UMRS_STAMP(p.c.counters, 0);
   scan_fan(sm, p.c, fan, sm.obj, p.L_obj, skip_lo, skip_hi, p.c.ranges + off,
            p.c.hit_idx ? p.c.hit_idx + off : nullptr, post);
 }

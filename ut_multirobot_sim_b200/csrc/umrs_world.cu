@@ -204,7 +204,7 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (ok()) e = dalloc(&w->d_fan_params, WR);
   if (ok()) e = dalloc(&w->d_obj_lines, (size_t)w->W * w->L_obj);
   if (ok()) e = dalloc(&w->d_pose, WR * 3);
-  if (ok()) e = dalloc(&w->d_counters, (size_t)8);
+  if (ok()) e = dalloc(&w->d_counters, (size_t)kNumCounters);
   if (ok()) e = dalloc(&w->d_stats, (size_t)4);
   if (ok()) e = cudaMemcpy(w->d_robots, w->robots.data(), sizeof(umrs_robot_params) * w->R, cudaMemcpyHostToDevice);
   if (ok() && w->H) e = cudaMemcpy(w->d_humans, w->humans.data(), sizeof(umrs_human_params) * w->H, cudaMemcpyHostToDevice);
@@ -214,7 +214,7 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (ok()) e = cudaMemcpy(w->d_ray_off, w->ray_off.data(), sizeof(int32_t) * w->ray_off.size(), cudaMemcpyHostToDevice);
   if (ok()) e = cudaMemcpy(w->d_num_rays, w->num_rays.data(), sizeof(int32_t) * w->R, cudaMemcpyHostToDevice);
   if (ok()) e = cudaMemset(w->d_static, 0, sizeof(float) * (WO * 3 > 0 ? WO * 3 : 1));
-  if (ok()) e = cudaMemset(w->d_counters, 0, sizeof(unsigned long long) * 8);
+  if (ok()) e = cudaMemset(w->d_counters, 0, sizeof(unsigned long long) * kNumCounters);
   if (ok()) e = cudaMemset(w->d_ranges, 0, sizeof(float) * n_rays);
   if (!ok()) {
     const int rc = capi_cuda_fail(e, "umrs_world_create");
@@ -389,7 +389,7 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   p.laser_noise = w->desc.laser_noise_enabled;
   p.motion_noise = w->desc.motion_noise_enabled;
   if (w->counters_on && first == 0)
-    UMRS_CUDA(cudaMemsetAsync(w->d_counters, 0, sizeof(unsigned long long) * 8, stream));
+    UMRS_CUDA(cudaMemsetAsync(w->d_counters, 0, sizeof(unsigned long long) * kNumCounters, stream));
   UMRS_CUDA(launch_world_step(p, stream));
   if (last) {
     w->cur ^= 1;
@@ -489,6 +489,13 @@ int umrs_world_read_counters_ex(umrs_world* w, uint64_t out8[8]) {
   if (w == NULL || out8 == NULL) return UMRS_ERR_INVALID;
   UMRS_CUDA(cudaDeviceSynchronize());
   UMRS_CUDA(cudaMemcpy(out8, w->d_counters, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
+  return UMRS_OK;
+}
+
+int umrs_world_read_phase_cycles(umrs_world* w, uint64_t out8[8]) {
+  if (w == NULL || out8 == NULL) return UMRS_ERR_INVALID;
+  UMRS_CUDA(cudaDeviceSynchronize());
+  UMRS_CUDA(cudaMemcpy(out8, w->d_counters + 8, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
   return UMRS_OK;
 }
 
