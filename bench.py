@@ -229,6 +229,8 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
     torch.cuda.set_device(local_rank)
+    from ut_multirobot_sim_b200 import shard
+    cpus = None if os.environ.get("UMRS_NO_BIND") else shard.bind_host_to_gpu(local_rank)
     lib = _lib.load()
     _lib.check(lib.umrs_set_device(local_rank), "umrs_set_device")
     if world_size > 1:
@@ -308,7 +310,7 @@ def run_b200(args):
     world.step_device(d_cmds[0].data_ptr(), None, sp)
     cnt = world.read_counters()
     world.enable_counters(False)
-    stats = world.stats()
+    stats = shard.reduce_stats(world.stats())   # the only cross-GPU exchange (NCCL), after the timed region
 
     total_rays = rays_per_step * world_size
     value = total_rays * K / (ms_dev * 1e-3)
@@ -323,6 +325,19 @@ def run_b200(args):
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     alg_bytes = rays_per_step * 4 + W * (64 * 2 + 12 + 16 + 12)  # ranges out + state r/w + cmd + fan + pose
+    # per-launch facts of the committed `ncu --set full` capture of this workload (profiles/):
+    # DRAM traffic and warp instructions executed (both properties of the launch, not of a clock)
+    traffic, issue = None, None
+    try:
+        facts = json.load(open(os.path.join(ROOT, "profiles", "r1_kernel_facts.json")))
+        if facts.get("worlds") == W and args.map_segments == 1024:
+            traffic = facts["dram_bytes_read"] + facts["dram_bytes_write"]
+            ginst = facts["inst_executed"] / kernel_s / 1e9
+            peak_ginst = 148 * 4 * 1.965            # 4 schedulers per SM, one warp instruction per clock each
+            issue = {"achieved_ginst_per_s": ginst, "peak_ginst_per_s": peak_ginst, "frac": ginst / peak_ginst,
+                     "source": "smsp__inst_executed.sum of the committed capture / live launch time; peak = 148 SM x 4 x 1.965 GHz"}
+    except Exception:
+        pass
     out = {
         "metric": "lidar_rays_per_sec", "value": value, "unit": "rays/s",
         "n_gpus": world_size, "steps": K, "warmup": Wm, "ms_per_step": ms_dev / K,
@@ -339,7 +354,8 @@ def run_b200(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": FP32_PEAK_TFLOPS,
-                     "unit": "TFLOP/s", "frac": achieved_tflops / FP32_PEAK_TFLOPS, "traffic": None,
+                     "unit": "TFLOP/s", "frac": achieved_tflops / FP32_PEAK_TFLOPS, "traffic": traffic,
+                     "issue": issue,
                      "kernel": "k_world_step", "tests_per_launch": int(tests),
                      "tests_per_ray": tests / rays_per_step,
                      "segs_prepared_per_fan": cnt["segs_prepared"] / W,
@@ -349,6 +365,7 @@ def run_b200(args):
                              "frac": alg_bytes / kernel_s / 1e9 / hbm_peak,
                              "peak_source": "measured" if "hbm_gbs" in peaks else "fallback"}},
         "stats": stats,
+        "host": {"cpus_bound": None if cpus is None else len(cpus), "cpu_count": os.cpu_count()},
     }
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
         fans = world.fan_params().reshape(-1, 4)
