@@ -1,0 +1,189 @@
+"""Per-config parity report ("report the tier-A agreement rate per config next
+to the tier-B exactness").  For BASELINE configs 1-4 the GPU scan is compared ray by ray with
+
+  tier B  the oracle's per-ray minimum (oracle/umrs_oracle.c): the GPU contract -- every ray within
+          1e-5 relative, > 99.9 % bit-identical, hit index equal but for certified ties;
+  tier A  the UNMODIFIED reference GetPredictedScan (oracle/_ref): the agreement rate is reported,
+          and every disagreeing ray must be one where tier B disagrees with tier A too (the
+          documented TrimOcclusion classes D1-D6), never a ray the GPU alone gets differently.
+
+The numbers are asserted here and written to gpurun_out/parity_report.json for DESIGN.md."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import ut_multirobot_sim_b200 as umrs
+from tests.test_gpu_scan import check_against_tierb
+from ut_multirobot_sim_b200 import synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+D135 = np.float32(np.pi * 135.0 / 180.0)
+REPORT = {}
+
+
+def _compare(oracle, refmap, segs, obj, fans, range_max, n, r_gpu, i_gpu, skip=None):
+    """Returns the report row for a set of fans; asserts the contract per fan."""
+    rays = exact = ties = a_agree = b_vs_a = gpu_only = 0
+    worst_b = 0.0
+    for k, f in enumerate(fans):
+        sk = (0, 0) if skip is None else skip[k]
+        e, t = check_against_tierb(oracle, segs, obj, f, range_max, n, r_gpu[k], i_gpu[k], skip=sk)
+        exact += e
+        ties += t
+        rays += n
+        r_b, _ = oracle.scan_tierb(segs, obj, f[:2], range_max, f[2], f[3], n, skip=sk)
+        worst_b = max(worst_b, float((np.abs(r_gpu[k].astype(np.float64) - r_b) /
+                                      np.maximum(np.abs(r_b.astype(np.float64)), 1e-9)).max()))
+        if refmap is None:
+            continue
+        o = np.zeros((0, 4), np.float32) if obj is None else np.asarray(obj, np.float32).reshape(-1, 4)
+        if sk[1] > sk[0]:
+            o = np.concatenate([o[:sk[0]], o[sk[1]:]])
+        refmap.set_object_lines(o)
+        r_a = refmap.predicted_scan(f[:2], 0.4, range_max, f[2], f[3], n)
+        den = np.maximum(np.abs(r_a.astype(np.float64)), 1e-9)
+        rel_ga = np.abs(r_gpu[k].astype(np.float64) - r_a) / den
+        rel_ba = np.abs(r_b.astype(np.float64) - r_a) / den
+        a_agree += int((rel_ga <= 1e-5).sum())
+        b_vs_a += int((rel_ba <= 1e-5).sum())
+        gpu_only += int(((rel_ga > 2e-5) & (rel_ba <= 1e-5)).sum())
+    row = {"fans": len(fans), "rays": rays, "bit_identical_to_tier_b": exact / rays,
+           "max_rel_vs_tier_b": worst_b, "certified_ties": ties}
+    if refmap is not None:
+        row.update({"within_1e-5_of_reference": a_agree / rays,
+                    "tier_b_within_1e-5_of_reference": b_vs_a / rays,
+                    "rays_only_the_gpu_gets_differently": gpu_only})
+        assert gpu_only == 0
+    assert exact / rays > 0.999 and worst_b <= 1e-5
+    return row
+
+
+def _ref_or_none():
+    from tests import oracle_lib
+    return oracle_lib.load_ref()
+
+
+def test_config1_single_car_on_the_campus_map(oracle):
+    segs = umrs.map_cleanup(synth.floorplan_segments(1500, 200.0, 1234))
+    vmap = umrs.VectorMap(lines=segs)
+    poses = synth.sample_free_poses(segs, 64, 200.0, 1234)
+    fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - D135, poses[:, 2] + D135], 1).astype(np.float32)
+    r = np.empty((64, 1081), np.float32)
+    i = np.empty((64, 1081), np.int32)
+    for k, f in enumerate(fans):
+        r[k], i[k] = vmap.GetPredictedScan(f[:2], 0.4, 100.0, f[2], f[3], 1081, return_index=True)
+    ref = _ref_or_none()
+    refmap = None if ref is None else ref.map_from_segments(segs, False)
+    REPORT["config1"] = _compare(oracle, refmap, segs, None, fans, 100.0, 1081, r, i)
+
+
+def test_config2_crowded_world(oracle):
+    extent = 60.0
+    segs = umrs.map_cleanup(synth.floorplan_segments(300, extent=extent, seed=1234))
+    vmap = umrs.VectorMap(lines=segs)
+    rps = [umrs.default_robot("ut_jackal") for _ in range(3)] + [umrs.default_robot("bwibot") for _ in range(3)] + \
+          [umrs.default_robot("cobot") for _ in range(2)]
+    hps = [umrs.default_human() for _ in range(16)]
+    W, R = 4, 8
+    world = umrs.World(vmap, rps, W, humans=hps, static_objects=1, seed=9)
+    free = synth.sample_free_poses_fast(segs, W * R, extent, seed=21, clearance=0.6).reshape(W, R, 3)
+    hs = synth.sample_free_poses_fast(segs, W * 32, extent, seed=22).reshape(W, 32, 3)
+    st = synth.sample_free_poses_fast(segs, W, extent, seed=23).reshape(W, 1, 3)
+    for arr in (free, hs, st):      # pull everybody towards robot 0 so that bodies occlude scans
+        c = free[:, :1, :2]
+        arr[..., :2] = c + (arr[..., :2] - c) * 0.2
+    world.SetPose(free)
+    world.SetHumans(hs[:, :16], hs[:, 16:])
+    world.SetStaticObjects(st)
+    ranges, idx = world.Step(np.zeros((W, R, 3), np.float32), want_idx=True)
+    lines, fp = world.GetLines(), world.fan_params()
+    ref = _ref_or_none()
+    refmap = None if ref is None else ref.map_from_segments(segs, False)
+    n_obj = world.object_lines_per_world
+    rows = []
+    for r_i, rp in enumerate(rps):
+        hdr = world.scan_header(r_i)
+        sl = slice(hdr.ranges_offset, hdr.ranges_offset + hdr.num_rays)
+        # object lines: [static 4][humans 16 x 20][robot bodies]; robot r's own body is skipped
+        bodies = [k for k, q in enumerate(rps) if q.footprint_enabled]
+        own = (0, 0)
+        if rp.footprint_enabled:
+            b0 = 4 + 20 * 16 + 4 * bodies.index(r_i)
+            own = (b0, b0 + 4)
+        for w in range(W):
+            row = _compare(oracle, refmap, segs, lines[w], fp[w, r_i:r_i + 1], rp.laser.range_max, hdr.num_rays,
+                           ranges[w:w + 1, sl], idx[w:w + 1, sl], skip=[own])
+            rows.append(row)
+    assert n_obj == 4 + 20 * 16 + 4 * len([q for q in rps if q.footprint_enabled])
+    tot = sum(r["rays"] for r in rows)
+    agg = {"fans": len(rows), "rays": tot,
+           "bit_identical_to_tier_b": sum(r["bit_identical_to_tier_b"] * r["rays"] for r in rows) / tot,
+           "max_rel_vs_tier_b": max(r["max_rel_vs_tier_b"] for r in rows),
+           "certified_ties": sum(r["certified_ties"] for r in rows)}
+    if refmap is not None:
+        for k in ("within_1e-5_of_reference", "tier_b_within_1e-5_of_reference"):
+            agg[k] = sum(r[k] * r["rays"] for r in rows) / tot
+        agg["rays_only_the_gpu_gets_differently"] = sum(r["rays_only_the_gpu_gets_differently"] for r in rows)
+    REPORT["config2"] = agg
+
+
+@pytest.mark.parametrize("M", [64, 256, 1024])
+def test_config3_batched_worlds(oracle, M):
+    segs = umrs.map_cleanup(synth.floorplan_segments(M, extent=200.0, seed=1234))
+    vmap = umrs.VectorMap(lines=segs)
+    car = umrs.default_robot("ut_automata")
+    W = 4096
+    world = umrs.World(vmap, [car], W, seed=42)
+    world.SetPose(synth.sample_free_poses_fast(segs, W, 200.0, seed=11).reshape(W, 1, 3))
+    ranges, idx = world.Step(synth.ackermann_commands(W, 1, 0), want_idx=True)
+    fp = world.fan_params()
+    pick = np.arange(0, W, W // 48)
+    ref = _ref_or_none()
+    refmap = None if ref is None else ref.map_from_segments(segs, False)
+    own = None
+    lines = None
+    if world.object_lines_per_world:
+        lines = world.GetLines()
+    rows = []
+    for w in pick:
+        obj = None if lines is None else lines[w]
+        sk = None if lines is None else [(0, world.object_lines_per_world)]
+        rows.append(_compare(oracle, refmap, segs, obj, fp[w], car.laser.range_max, 1081,
+                             ranges[w:w + 1], idx[w:w + 1], skip=sk))
+    tot = sum(r["rays"] for r in rows)
+    agg = {"fans": len(rows), "rays": tot, "map_segments": int(len(segs)),
+           "bit_identical_to_tier_b": sum(r["bit_identical_to_tier_b"] * r["rays"] for r in rows) / tot,
+           "max_rel_vs_tier_b": max(r["max_rel_vs_tier_b"] for r in rows),
+           "certified_ties": sum(r["certified_ties"] for r in rows)}
+    if refmap is not None:
+        for k in ("within_1e-5_of_reference", "tier_b_within_1e-5_of_reference"):
+            agg[k] = sum(r[k] * r["rays"] for r in rows) / tot
+        agg["rays_only_the_gpu_gets_differently"] = sum(r["rays_only_the_gpu_gets_differently"] for r in rows)
+    REPORT["config3_M%d" % M] = agg
+
+
+def test_config4_large_map_sample(oracle):
+    """100k segments: the reference's render stops at 2000 candidates (D4), tier B only."""
+    segs = synth.cityblock_segments(100000, extent=2000.0, seed=99)
+    vmap = umrs.VectorMap(lines=segs)
+    clean = vmap.lines
+    rng = np.random.default_rng(4)
+    poses = np.stack([rng.uniform(100, 1900, 925), rng.uniform(100, 1900, 925),
+                      rng.uniform(-np.pi, np.pi, 925)], 1).astype(np.float32)
+    fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - D135, poses[:, 2] + D135], 1).astype(np.float32)
+    r, i = vmap.ScanBatch(fans, 100.0, 1081, return_index=True)
+    pick = np.arange(0, 925, 925 // 9)[:10]
+    REPORT["config4"] = _compare(oracle, None, clean, None, fans[pick], 100.0, 1081, r[pick], i[pick])
+
+
+def test_write_report():
+    assert len(REPORT) >= 5, "run the whole module"
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "parity_report.json"), "w") as f:
+            json.dump(REPORT, f, indent=1)
+    for k, v in REPORT.items():
+        print(k, json.dumps(v))
