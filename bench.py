@@ -327,13 +327,16 @@ def run_b200(args):
     alg_bytes = rays_per_step * 4 + W * (64 * 2 + 12 + 16 + 12)  # ranges out + state r/w + cmd + fan + pose
     # per-launch facts of the committed `ncu --set full` capture of this workload (profiles/):
     # DRAM traffic and warp instructions executed (both properties of the launch, not of a clock)
-    traffic, issue = None, None
+    traffic, issue, pipes = None, None, None
     try:
         facts = json.load(open(os.path.join(ROOT, "profiles", "r1_kernel_facts.json")))
         if facts.get("worlds") == W and args.map_segments == 1024:
             traffic = facts["dram_bytes_read"] + facts["dram_bytes_write"]
             ginst = facts["inst_executed"] / kernel_s / 1e9
             peak_ginst = 148 * 4 * 1.965            # 4 schedulers per SM, one warp instruction per clock each
+            pipes = {k: facts[k] for k in ("fma_pipe_pct", "alu_pipe_pct", "xu_pipe_pct", "lsu_pipe_pct",
+                                           "fp64_pipe_pct", "smem_wavefronts_pct_of_peak", "issue_active_pct")
+                     if k in facts}
             issue = {"achieved_ginst_per_s": ginst, "peak_ginst_per_s": peak_ginst, "frac": ginst / peak_ginst,
                      "source": "smsp__inst_executed.sum of the committed capture / live launch time; peak = 148 SM x 4 x 1.965 GHz"}
     except Exception:
@@ -355,7 +358,8 @@ def run_b200(args):
         "clocks": clocks,
         "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": FP32_PEAK_TFLOPS,
                      "unit": "TFLOP/s", "frac": achieved_tflops / FP32_PEAK_TFLOPS, "traffic": traffic,
-                     "issue": issue,
+                     "issue": issue, "ncu_pipe_utilisation": pipes,
+                     "brute_force_equivalent_tflops": FLOPS_PER_TEST * cnt["segs_prepared"] * N_RAYS / kernel_s / 1e12,
                      "kernel": "k_world_step", "tests_per_launch": int(tests),
                      "tests_per_ray": tests / rays_per_step,
                      "segs_prepared_per_fan": cnt["segs_prepared"] / W,

@@ -163,6 +163,11 @@ int umrs_map_cleanup(const float* segs_xyxy, int32_t n, float* out_xyxy,
 int umrs_map_cleanup_ex(const float* segs_xyxy, int32_t n, float* out_xyxy, int32_t cap,
                         int32_t* n_out, int32_t algorithm);
 
+/* The same eight counters for the scan entry points below (for the
+ * grid walk report rows visited and bytes of segment data fetched per ray). */
+int umrs_map_enable_counters(umrs_map* map, int32_t on);
+int umrs_map_read_counters(umrs_map* map, uint64_t out8[8]);
+
 /* ---- drop-in scan -------------------------------------------------------------
  * Same seven arguments as VectorMap::GetPredictedScan (vector_map.h:66-72) plus
  * the object lines the reference keeps in VectorMap::object_lines
@@ -272,7 +277,8 @@ int umrs_world_read_counters(umrs_world* world, uint64_t* ray_seg_tests,
 
 /* All eight counters of the last step: {ray_seg_tests, segs_prepared,
  * chunk_seg_pairs, passes (summed over fans), tie sweeps, spilled-candidate
- * list entries, fans that swept every slot, spare}. */
+ * list entries, fans that swept every slot, source segments streamed by the
+ * gather (low 40 bits) | source rows visited << 40}. */
 int umrs_world_read_counters_ex(umrs_world* world, uint64_t out8[8]);
 /* Development builds only (-DUMRS_PHASE_TIMING): clock cycles of every fan CTA's critical
  * path per phase, summed over the fans of the last step: {world phase A, setup, gather,

@@ -108,9 +108,20 @@ def config4():
     t0 = time.perf_counter()
     vmap.ScanBatch(fans, 100.0, 1081)
     dh = time.perf_counter() - t0
+    vmap.enable_counters(True)       # rows visited and segment bytes fetched per ray (grid walk)
+    run()
+    cnt = vmap.read_counters()
+    vmap.enable_counters(False)
+    rays = n_fans * 1081
     print(json.dumps({"config": 4, "what": "100k-segment city-block map (2 km), 925 fans x 1081 rays, uniform-grid rows (K2)",
-                      "ms_per_step": ms, "rays_per_s": n_fans * 1081 / ms * 1e3,
-                      "host_buffer_ms": dh * 1e3, "host_buffer_rays_per_s": n_fans * 1081 / dh}))
+                      "ms_per_step": ms, "rays_per_s": rays / ms * 1e3,
+                      "host_buffer_ms": dh * 1e3, "host_buffer_rays_per_s": rays / dh,
+                      "grid_rows_per_fan": cnt["source_rows"] / n_fans,
+                      "source_segments_per_fan": cnt["source_segments"] / n_fans,
+                      "segment_bytes_fetched_per_ray": cnt["source_segments"] * 20.0 / rays,
+                      "segs_prepared_per_fan": cnt["segs_prepared"] / n_fans,
+                      "tests_per_ray": cnt["ray_seg_tests"] / rays,
+                      "passes_per_fan": cnt["passes"] / n_fans}))
 
 
 if __name__ == "__main__":

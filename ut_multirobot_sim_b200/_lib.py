@@ -93,6 +93,8 @@ SIGNATURES = {
     "umrs_map_num_segments": (C.c_int, [_P, _I]),
     "umrs_map_get_segments": (C.c_int, [_P, _F, C.c_int32]),
     "umrs_map_cleanup": (C.c_int, [_F, C.c_int32, _F, C.c_int32, _I]),
+    "umrs_map_enable_counters": (C.c_int, [_P, C.c_int32]),
+    "umrs_map_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "umrs_map_cleanup_ex": (C.c_int, [_F, C.c_int32, _F, C.c_int32, _I, C.c_int32]),
     "umrs_predicted_scan": (C.c_int, [_P, _F, C.c_int32, C.c_float, C.c_float, C.c_float,
                                       C.c_float, C.c_float, C.c_float, C.c_int32, _F, _I]),

@@ -132,6 +132,17 @@ class VectorMap:
             float(range_max), int(num_rays), _fp(ranges), _ip(idx)), "umrs_scan_batch")
         return (ranges, idx) if return_index else ranges
 
+    def enable_counters(self, on=True):
+        check(self._lib.umrs_map_enable_counters(self._h, int(on)), "umrs_map_enable_counters")
+
+    def read_counters(self):
+        """Work accounting of the last scan call (see World.read_counters)."""
+        ex = (C.c_uint64 * 8)()
+        check(self._lib.umrs_map_read_counters(self._h, ex), "umrs_map_read_counters")
+        return {"ray_seg_tests": ex[0], "segs_prepared": ex[1], "chunk_seg_pairs": ex[2], "passes": ex[3],
+                "tie_sweeps": ex[4], "spilled_entries": ex[5], "sweep_all_fans": ex[6],
+                "source_segments": ex[7] & ((1 << 40) - 1), "source_rows": ex[7] >> 40}
+
     def _free(self):
         if self._h:
             self._lib.umrs_map_destroy(self._h)
@@ -251,7 +262,8 @@ class World:
         ex = (C.c_uint64 * 8)()
         check(self._lib.umrs_world_read_counters_ex(self._h, ex), "read_counters_ex")
         return {"ray_seg_tests": a.value, "segs_prepared": b.value, "chunk_seg_pairs": c.value,
-                "passes": ex[3], "tie_sweeps": ex[4], "spilled_entries": ex[5], "sweep_all_fans": ex[6]}
+                "passes": ex[3], "tie_sweeps": ex[4], "spilled_entries": ex[5], "sweep_all_fans": ex[6],
+                "source_segments": ex[7] & ((1 << 40) - 1), "source_rows": ex[7] >> 40}
 
     def phase_cycles(self):
         """Dev builds (-DUMRS_PHASE_TIMING): summed critical-path cycles per phase; zeros otherwise."""

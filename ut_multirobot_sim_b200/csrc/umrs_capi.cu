@@ -104,6 +104,9 @@ struct umrs_map {
   float4* d_obj = nullptr;  size_t obj_cap = 0;
   float* d_ranges = nullptr; size_t ranges_cap = 0;
   int32_t* d_idx = nullptr;  size_t idx_cap = 0;
+  // work accounting of the scan entry points (umrs_map_enable_counters)
+  unsigned long long* d_counters = nullptr;
+  bool counters_on = false;
 };
 
 // Host-side, one-time (like VectorMap::Load/Cleanup): bin every segment by the
@@ -306,6 +309,7 @@ int umrs_map_destroy(umrs_map* m) {
   if (m->d_obj) cudaFree(m->d_obj);
   if (m->d_ranges) cudaFree(m->d_ranges);
   if (m->d_idx) cudaFree(m->d_idx);
+  if (m->d_counters) cudaFree(m->d_counters);
   if (m->stream) cudaStreamDestroy(m->stream);
   delete m;
   return UMRS_OK;
@@ -330,6 +334,25 @@ int umrs_map_set_scan_kernel(umrs_map* m, int32_t force) {
 }
 
 // ================================== scans =========================================
+int umrs_map_enable_counters(umrs_map* m, int32_t on) {
+  if (m == NULL) return UMRS_ERR_INVALID;
+  if (on && m->d_counters == nullptr) {
+    UMRS_CUDA(cudaMalloc(&m->d_counters, sizeof(unsigned long long) * kNumCounters));
+    UMRS_CUDA(cudaMemset(m->d_counters, 0, sizeof(unsigned long long) * kNumCounters));
+  }
+  m->counters_on = on != 0;
+  return UMRS_OK;
+}
+
+int umrs_map_read_counters(umrs_map* m, uint64_t out8[8]) {
+  if (m == NULL || out8 == NULL) return UMRS_ERR_INVALID;
+  memset(out8, 0, sizeof(uint64_t) * 8);
+  if (m->d_counters == nullptr) return UMRS_OK;
+  UMRS_CUDA(cudaDeviceSynchronize());
+  UMRS_CUDA(cudaMemcpy(out8, m->d_counters, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
+  return UMRS_OK;
+}
+
 int umrs_scan_batch_device(umrs_map* m, const float* obj_segs_dev, int32_t n_obj,
                            const float* fans_dev, int32_t n_fans, float range_max,
                            int32_t num_rays, float* ranges_dev, int32_t* hit_idx_dev,
@@ -354,6 +377,11 @@ int umrs_scan_batch_device(umrs_map* m, const float* obj_segs_dev, int32_t n_obj
   p.c.ranges = ranges_dev;
   p.c.hit_idx = hit_idx_dev;
   p.c.counters = nullptr;
+  if (m->counters_on && m->d_counters != nullptr) {
+    p.c.counters = m->d_counters;
+    UMRS_CUDA(cudaMemsetAsync(m->d_counters, 0, sizeof(unsigned long long) * kNumCounters,
+                              stream ? (cudaStream_t)stream : m->stream));
+  }
   p.obj_segs = reinterpret_cast<const float4*>(obj_segs_dev);
   p.n_obj = n_obj;
   p.fans = reinterpret_cast<const float4*>(fans_dev);

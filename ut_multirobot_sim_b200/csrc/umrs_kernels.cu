@@ -699,7 +699,11 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
       __syncthreads();
     }
   }
-  if (c.counters != nullptr && threadIdx.x == 0) atomicAdd(c.counters + 3, (unsigned long long)pass);
+  if (c.counters != nullptr && threadIdx.x == 0) {
+    atomicAdd(c.counters + 3, (unsigned long long)pass);
+    // source segments streamed by the gather (16 B each) | source rows, packed: rows << 40
+    atomicAdd(c.counters + 7, (unsigned long long)v_total | ((unsigned long long)sm.ctl[kCtlNRows] << 40));
+  }
   finalise(sm, fan, ranges, hit_idx, post);
 #ifdef UMRS_PHASE_TIMING
   __syncthreads();
