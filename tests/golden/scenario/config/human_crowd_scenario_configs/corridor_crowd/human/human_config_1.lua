@@ -3,13 +3,13 @@ hu_radius = 0.1
 hu_num_segments = 20
 
 -- Human start position
-hu_start_x = 9.0
-hu_start_y = 15.0
+hu_start_x = -8
+hu_start_y = -4.5
 hu_start_theta = 0.
 
 -- Human goal position
-hu_goal_x = 29
-hu_goal_y = 14.6
+hu_goal_x = 12
+hu_goal_y = -4
 hu_goal_theta = 0.
 
 -- Human speed information

@@ -3,13 +3,13 @@ hu_radius = 0.1
 hu_num_segments = 20
 
 -- Human start position
-hu_start_x = 10.0
-hu_start_y = 22.0
+hu_start_x = 2.0
+hu_start_y = 6.75
 hu_start_theta = 0.
 
 -- Human goal position
-hu_goal_x = 30.0
-hu_goal_y = 21.0
+hu_goal_x = 2.5
+hu_goal_y = -14.0
 hu_goal_theta = 0.
 
 -- Human speed information

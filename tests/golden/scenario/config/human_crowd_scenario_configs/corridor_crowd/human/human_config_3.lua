@@ -3,13 +3,13 @@ hu_radius = 0.1
 hu_num_segments = 20
 
 -- Human start position
-hu_start_x = 30.0
-hu_start_y = 21.9
+hu_start_x = 3
+hu_start_y = -14
 hu_start_theta = 0.
 
 -- Human goal position
-hu_goal_x = 10.0
-hu_goal_y = 22.0
+hu_goal_x = 3.5
+hu_goal_y = 7
 hu_goal_theta = 0.
 
 -- Human speed information

@@ -3,13 +3,13 @@ hu_radius = 0.1
 hu_num_segments = 20
 
 -- Human start position
-hu_start_x = 28.0
-hu_start_y = 14.7
+hu_start_x = -6.5
+hu_start_y = 1.125
 hu_start_theta = 0.
 
 -- Human goal position
-hu_goal_x = 8.0
-hu_goal_y = 15.0
+hu_goal_x = 9.75
+hu_goal_y = 1.0
 hu_goal_theta = 0.
 
 -- Human speed information

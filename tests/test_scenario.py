@@ -1,5 +1,5 @@
 """Scenario generator parity: ut_multirobot_sim_b200.scenario against the
-files the UNMODIFIED reference scripts/generate_config.py wrote for scripts/example.yml
+files the UNMODIFIED reference scripts/generate_config.py wrote for tests/golden/scenario/crowd.yml
 (tests/golden/scenario, made by tests/golden/make_scenario_golden.py), the round trip through
 the config evaluator, and the batched world descriptors (seeding, sharding); one GPU test
 steps a scenario batch and checks humans and scans against the oracle."""
@@ -12,7 +12,7 @@ import pytest
 from ut_multirobot_sim_b200 import scenario
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scenario")
-EXAMPLE = os.path.join(GOLD, "example.yml")
+EXAMPLE = os.path.join(GOLD, "crowd.yml")
 
 
 def _tree(root):
@@ -28,19 +28,21 @@ def test_generated_files_equal_the_reference_scripts_output(tmp_path):
     init = scenario.generate_config(EXAMPLE, str(tmp_path))
     want = _tree(os.path.join(GOLD, "config"))
     got = _tree(str(tmp_path / "config"))
-    assert sorted(got) == sorted(want) and len(want) == 5
+    assert sorted(got) == sorted(want) and len(want) == 7
     for name in want:
         assert got[name] == want[name], name          # byte for byte, "\n\r" separators included
-    assert init.endswith("config/human_crowd_scenario_configs/example_scenario/init_config.lua")
+    assert init.endswith("config/human_crowd_scenario_configs/corridor_crowd/init_config.lua")
 
 
 def test_yaml_scalars_are_formatted_like_the_reference(tmp_path):
-    """The reference str()-formats the YAML scalars: an int stays '29', a float '14.6'."""
+    """The reference str()-formats the YAML scalars: an int stays '12', a float '-4.5'."""
     scn = scenario.load_yaml(EXAMPLE)
-    assert scn.human_start_goal_positions[2][1][0] == 29 and isinstance(scn.human_start_goal_positions[2][1][0], int)
+    assert scn.human_start_goal_positions[1][1][0] == 12 and isinstance(scn.human_start_goal_positions[1][1][0], int)
+    assert scn.start_y == -11 and isinstance(scn.start_y, int)
     scenario.generate_config(scn, str(tmp_path))
-    txt = open(tmp_path / "config/human_crowd_scenario_configs/example_scenario/human/human_config_2.lua").read()
-    assert "hu_goal_x = 29\n" in txt and "hu_goal_y = 14.6\n" in txt
+    txt = open(tmp_path / "config/human_crowd_scenario_configs/corridor_crowd/human/human_config_1.lua").read()
+    assert "hu_goal_x = 12\n" in txt and "hu_start_y = -4.5\n" in txt
+    assert "start_y = -11\n" in open(tmp_path / "config/human_crowd_scenario_configs/corridor_crowd/init_config.lua").read()
 
 
 def test_missing_keys_are_reported(tmp_path):
@@ -60,11 +62,11 @@ def test_generated_files_load_through_the_config_evaluator(tmp_path):
     scn = scenario.load_yaml(EXAMPLE)
     ours = scenario.load_scenario_configs(scenario.generate_config(scn, str(tmp_path)), str(tmp_path))
     gold = scenario.load_scenario_configs(
-        os.path.join(GOLD, "config/human_crowd_scenario_configs/example_scenario/init_config.lua"), GOLD)
+        os.path.join(GOLD, "config/human_crowd_scenario_configs/corridor_crowd/init_config.lua"), GOLD)
     for ls in (ours, gold):
-        assert ls.map_name == "maps/GDC3.txt"
-        assert np.array_equal(ls.start_pose, np.array([13.016267, 21.534157, 0.0], np.float32))
-        assert len(ls.humans) == 4 and ls.human_files[3].endswith("human/human_config_3.lua")
+        assert ls.map_name == "maps/AHG2.txt"
+        assert np.array_equal(ls.start_pose, np.array([4.25, -11, 1.5707963], np.float32))
+        assert len(ls.humans) == 6 and ls.human_files[3].endswith("human/human_config_3.lua")
         for hp, (s, g) in zip(ls.humans, scn.human_start_goal_positions):
             assert (hp.start_x, hp.start_y) == (np.float32(s[0]), np.float32(s[1]))
             assert (hp.goal_x, hp.goal_y) == (np.float32(g[0]), np.float32(g[1]))
@@ -79,10 +81,10 @@ def test_generated_files_load_through_the_config_evaluator(tmp_path):
 def test_world_batch_seeding_and_sharding(tmp_path):
     scn = scenario.load_yaml(EXAMPLE)
     full = scenario.world_batch(scn, 64, seed=7)
-    assert full.robot_pose.shape == (64, 1, 3) and full.human_start.shape == (64, 4, 3)
+    assert full.robot_pose.shape == (64, 1, 3) and full.human_start.shape == (64, 6, 3)
     # world 0 is the scenario itself
-    assert np.array_equal(full.robot_pose[0, 0], np.array([13.016267, 21.534157, 0.0], np.float32))
-    assert np.array_equal(full.human_goal[0, 2, :2], np.array([29, 14.6], np.float32))
+    assert np.array_equal(full.robot_pose[0, 0], np.array([4.25, -11, 1.5707963], np.float32))
+    assert np.array_equal(full.human_goal[0, 2, :2], np.array([2.5, -14.0], np.float32))
     # the others are perturbed within the stated bounds, and differ from each other
     d = full.robot_pose[1:, 0, :2] - full.robot_pose[0, 0, :2]
     assert (np.abs(d) <= 0.5 + 1e-5).all() and np.abs(d).min() > 0
@@ -99,25 +101,25 @@ def test_world_batch_seeding_and_sharding(tmp_path):
     # file round trip + the command line
     full.save(str(tmp_path / "b.npz"))
     back = scenario.WorldBatch.load(str(tmp_path / "b.npz"))
-    assert back.map_name == "maps/GDC3.txt" and np.array_equal(back.human_goal, full.human_goal)
+    assert back.map_name == "maps/AHG2.txt" and np.array_equal(back.human_goal, full.human_goal)
     scenario.main(["--config-file", EXAMPLE, "--out-root", str(tmp_path), "--worlds", "8", "--seed", "7"])
     cli = scenario.WorldBatch.load(
-        str(tmp_path / "config/human_crowd_scenario_configs/example_scenario/world_batch.npz"))
+        str(tmp_path / "config/human_crowd_scenario_configs/corridor_crowd/world_batch.npz"))
     assert np.array_equal(cli.robot_pose, full.robot_pose[:8])
 
 
 @pytest.mark.gpu
 def test_scenario_batch_steps_on_the_gpu_like_the_oracle(oracle, tmp_path):
-    """16 variants of the example scenario (GDC3 is not in the repo: a 45 x 35 m room with
-    pillars stands in), one ut_automata car + the 4 walking humans per world, 60 steps:
-    human poses follow the restated HumanObject::Step (goal swap in Repeat mode included),
-    every scan equals the tier-B oracle over map + that world's human footprints."""
+    """16 variants of the golden scenario (its map file is not in the repo: a 30 x 30 m hall with
+    pillars stands in), one ut_automata car + the 6 walking humans per world, 60 steps:
+    human poses follow the restated HumanObject::Step, every scan equals the tier-B oracle over
+    map + that world's human footprints."""
     import ut_multirobot_sim_b200 as umrs
     from tests import oracle_lib
     from tests.test_gpu_scan import check_against_tierb
     ls = scenario.load_scenario_configs(scenario.generate_config(EXAMPLE, str(tmp_path)), str(tmp_path))
-    walls = [[0, 0, 45, 0], [45, 0, 45, 35], [45, 35, 0, 35], [0, 35, 0, 0]]
-    for cx, cy in [(12, 10), (22, 18), (33, 10), (33, 28), (6, 28)]:
+    walls = [[-13, -18, 17, -18], [17, -18, 17, 12], [17, 12, -13, 12], [-13, 12, -13, -18]]
+    for cx, cy in [(-4, -9), (8, -9), (-4, 5), (8, 5), (14, -1)]:
         walls += [[cx - 1, cy - 1, cx + 1, cy - 1], [cx + 1, cy - 1, cx + 1, cy + 1],
                   [cx + 1, cy + 1, cx - 1, cy + 1], [cx - 1, cy + 1, cx - 1, cy - 1]]
     segs = umrs.map_cleanup(np.asarray(walls, np.float32))

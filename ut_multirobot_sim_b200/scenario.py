@@ -4,7 +4,7 @@ batched world descriptors -- thousands of seeded variants of one scenario, ready
 `World.SetPose / SetHumans`.
 
 `generate_config` writes byte-for-byte what the reference script writes (tests/golden/scenario
-holds the reference's own output for scripts/example.yml); `load_scenario_configs` reads those
+holds the reference script's own output for crowd.yml); `load_scenario_configs` reads those
 files back through the C-ABI config evaluator (umrs_config_*), i.e. the way
 Simulator::init/loadObject consume them (simulator.cpp:93-97,230-233).
 
