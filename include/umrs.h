@@ -197,6 +197,21 @@ int umrs_scan_batch_device(umrs_map* map, const float* obj_segs_dev, int32_t n_o
  * (K1), 1 = uniform grid (K2).  force: -1 auto, 0, 1. */
 int umrs_map_set_scan_kernel(umrs_map* map, int32_t force);
 
+/* Opt-in REFERENCE RENDER: GetPredictedScan exactly as the reference computes it --
+ * GetSceneLines, the SceneRender/TrimOcclusion visibility pass (vector_map.cpp:55-258)
+ * and "first rendered piece that covers the ray" (:458-476) -- so the ranges are
+ * bit-identical to the reference's own output, occlusion-trimming defects included
+ * (human_object.cpp:106).  The entry points above return the exact nearest hit instead
+ * and are ~100x faster; use this one where the reference's very numbers are needed.
+ * One warp per fan, O(L^2) per fan like the reference; no hit index (the reference has
+ * none).  The render stops at 2000 candidates like the reference (:221). */
+int umrs_scan_batch_reference_render(umrs_map* map, const float* obj_segs_xyxy, int32_t n_obj,
+                                     const float* fans, int32_t n_fans, float range_max,
+                                     int32_t num_rays, float* ranges_out);
+int umrs_scan_batch_reference_render_device(umrs_map* map, const float* obj_segs_dev, int32_t n_obj,
+                                            const float* fans_dev, int32_t n_fans, float range_max,
+                                            int32_t num_rays, float* ranges_dev, void* stream);
+
 /* ---- batched worlds ------------------------------------------------------------
  * W independent worlds stepping in lockstep; every world has the same robot
  * roster (robots[r] describes robot r of every world), H humans and O static

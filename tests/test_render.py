@@ -1,0 +1,124 @@
+"""The opt-in reference render (SceneRender + TrimOcclusion, vector_map.cpp:55-258).
+CPU: the restatement in csrc/umrs_render.h, built for the host, returns the compiled
+reference's rendered line list bit for bit.  GPU: umrs_scan_batch_reference_render returns the
+reference's GetPredictedScan ranges bit for bit (tier A), through the C-ABI."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from ut_multirobot_sim_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+D135 = np.float32(np.pi * 135.0 / 180.0)
+
+
+@pytest.fixture(scope="module")
+def harness(tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("render") / "librender_check.so")
+    subprocess.run(["g++", "-std=c++14", "-O2", "-ffp-contract=off", "-shared", "-fPIC", "-Wall", "-Werror",
+                    os.path.join(ROOT, "tests", "cpp", "render_check.cpp"), "-o", so], check=True)
+    lib = C.CDLL(so)
+    fp = C.POINTER(C.c_float)
+    lib.umrs_test_scene_render.argtypes = [fp, C.c_int, C.c_float, C.c_float, fp, C.c_int]
+    return lib
+
+
+def _maps():
+    import ut_multirobot_sim_b200 as umrs
+    rng = np.random.default_rng(5)
+    c = rng.uniform(5, 55, (220, 2))
+    d = rng.normal(0, 2.5, (220, 2))
+    clutter = umrs.map_cleanup(np.concatenate([c - d, c + d], 1).astype(np.float32))
+    return {"floorplan_300": (umrs.map_cleanup(synth.floorplan_segments(300, extent=60.0, seed=1234)), 60.0),
+            "floorplan_1024": (umrs.map_cleanup(synth.floorplan_segments(1024, extent=200.0, seed=1234)), 200.0),
+            "clutter": (clutter, 60.0)}
+
+
+def test_host_build_of_the_render_equals_the_reference_scene_render(harness, ref):
+    fp = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+    total = 0
+    for name, (segs, extent) in _maps().items():
+        rm = ref.map_from_segments(segs, False)
+        # humans (closed 20-gons) + a square: the shapes whose occlusion the reference gets wrong
+        th = np.linspace(0, 2 * np.pi, 21)
+        ring = np.stack([np.cos(th[:-1]), np.sin(th[:-1]), np.cos(th[1:]), np.sin(th[1:])], 1) * 0.3
+        obj = np.concatenate([ring + np.array([x, y, x, y]) for x, y in
+                              [(extent * 0.4, extent * 0.5), (extent * 0.55, extent * 0.45)]]).astype(np.float32)
+        rm.set_object_lines(obj)
+        poses = synth.sample_free_poses_fast(segs, 24, extent, seed=3)
+        for p in poses:
+            scene_in = rm.scene_lines(p[:2], 100.0)
+            out = np.empty((4000, 4), np.float32)
+            n = harness.umrs_test_scene_render(fp(scene_in), len(scene_in), p[0], p[1], fp(out), 4000)
+            want = np.empty((4000, 4), np.float32)
+            m = ref.lib.umrs_ref_scene_render(rm.h, p[0], p[1], 100.0, p[2] - D135, p[2] + D135, fp(want), 4000)
+            assert n == m, (name, n, m)
+            assert np.array_equal(out[:n].view(np.uint32), want[:m].view(np.uint32)), name
+            total += n
+    assert total > 1000
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["floorplan_300", "floorplan_1024", "clutter"])
+def test_gpu_reference_render_equals_the_reference_scan_bit_for_bit(ref, name):
+    """umrs_scan_batch_reference_render vs the UNMODIFIED reference GetPredictedScan on the same
+    map, object lines (closed human shapes) and fans: every range identical to the bit."""
+    import ut_multirobot_sim_b200 as umrs
+    segs, extent = _maps()[name]
+    vmap = umrs.VectorMap(lines=segs)
+    rm = ref.map_from_segments(segs, False)
+    th = np.linspace(0, 2 * np.pi, 21)
+    ring = np.stack([np.cos(th[:-1]), np.sin(th[:-1]), np.cos(th[1:]), np.sin(th[1:])], 1) * 0.3
+    poses = synth.sample_free_poses_fast(segs, 96, extent, seed=7)
+    # people standing around the first poses, so that scans see closed shapes up close
+    obj = np.concatenate([ring + np.array([x, y, x, y]) for x, y in poses[:6, :2] + 0.9]).astype(np.float32)
+    vmap.object_lines = obj
+    n = 1081
+    fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - D135, poses[:, 2] + D135], 1).astype(np.float32)
+    got = vmap.ScanBatchReferenceRender(fans, 100.0, n)
+    # the bridge takes object lines per fan: the same set for every fan
+    want = rm.scan_batch(fans, 0.4, 100.0, n, threads=4, obj=np.tile(obj, (len(fans), 1)),
+                         obj_offset=np.arange(len(fans) + 1, dtype=np.int32) * len(obj))
+    same = got.view(np.uint32) == want.view(np.uint32)
+    assert same.all(), "%d of %d rays differ, first fan %d" % ((~same).sum(), same.size, np.argwhere(~same)[0][0])
+    # the default scan (exact nearest hit) agrees with it on most rays, not all
+    exact = vmap.ScanBatch(fans, 100.0, n)
+    agree = (np.abs(exact - got) <= 1e-5 * np.abs(got)).mean()
+    assert agree > 0.9
+    print("%s: exact nearest hit within 1e-5 of the reference render on %.4f %% of rays" % (name, 100 * agree))
+
+
+@pytest.mark.gpu
+def test_gpu_reference_render_full_circle_jackal_and_the_2000_line_cap(ref):
+    """360-degree / 3601-ray fans (ut_jackal laser) and a clutter map whose render runs into the
+    reference's 2000-candidate cap (vector_map.cpp:221-223): still the reference's bits."""
+    import ut_multirobot_sim_b200 as umrs
+    rng = np.random.default_rng(9)
+    c = rng.uniform(0, 80, (2600, 2))
+    d = rng.normal(0, 0.6, (2600, 2))
+    raw = np.concatenate([c - d, c + d], 1).astype(np.float32)
+    segs = umrs.map_cleanup(raw)
+    assert len(segs) > 2300
+    vmap = umrs.VectorMap(lines=segs)
+    rm = ref.map_from_segments(segs, False)
+    poses = synth.sample_free_poses_fast(segs, 12, 80.0, seed=2, clearance=0.2)
+    lz = umrs.default_laser(jackal=True)
+    n = umrs.laser_num_rays(lz)
+    fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] + lz.angle_min, poses[:, 2] + lz.angle_max], 1).astype(np.float32)
+    got = vmap.ScanBatchReferenceRender(fans, 150.0, n)
+    want = rm.scan_batch(fans, 0.4, 150.0, n, threads=4)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_gpu_reference_render_argument_validation_and_empty_map():
+    import ut_multirobot_sim_b200 as umrs
+    vmap = umrs.VectorMap(lines=np.zeros((0, 4), np.float32))
+    r = vmap.ScanBatchReferenceRender(np.array([[0, 0, -1, 1]], np.float32), 30.0, 16)
+    assert np.array_equal(r, np.full((1, 16), 30.0, np.float32))
+    assert vmap.ScanBatchReferenceRender(np.zeros((0, 4), np.float32), 30.0, 16).shape == (0, 16)
+    with pytest.raises(umrs._lib.UmrsError):
+        vmap.ScanBatchReferenceRender(np.array([[0, 0, -1, 1]], np.float32), 30.0, 0)

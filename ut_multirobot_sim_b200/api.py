@@ -132,6 +132,17 @@ class VectorMap:
             float(range_max), int(num_rays), _fp(ranges), _ip(idx)), "umrs_scan_batch")
         return (ranges, idx) if return_index else ranges
 
+    def ScanBatchReferenceRender(self, fans, range_max, num_rays):
+        """The same fans through the reference's own render (SceneRender/TrimOcclusion +
+        first covering piece): bit-identical to the reference's GetPredictedScan output."""
+        fans = np.ascontiguousarray(fans, np.float32).reshape(-1, 4)
+        obj = _segs(self.object_lines)
+        ranges = np.empty((len(fans), num_rays), np.float32)
+        check(self._lib.umrs_scan_batch_reference_render(
+            self._h, _fp(obj) if len(obj) else None, len(obj), _fp(fans), len(fans),
+            float(range_max), int(num_rays), _fp(ranges)), "umrs_scan_batch_reference_render")
+        return ranges
+
     def enable_counters(self, on=True):
         check(self._lib.umrs_map_enable_counters(self._h, int(on)), "umrs_map_enable_counters")
 

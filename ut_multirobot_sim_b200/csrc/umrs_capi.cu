@@ -107,6 +107,10 @@ struct umrs_map {
   // work accounting of the scan entry points (umrs_map_enable_counters)
   unsigned long long* d_counters = nullptr;
   bool counters_on = false;
+  // scratch of the opt-in reference render (allocated on first use)
+  float4* d_render_lines = nullptr;
+  float4* d_render_scene = nullptr;
+  float* d_render_c = nullptr;
 };
 
 // Host-side, one-time (like VectorMap::Load/Cleanup): bin every segment by the
@@ -310,6 +314,9 @@ int umrs_map_destroy(umrs_map* m) {
   if (m->d_ranges) cudaFree(m->d_ranges);
   if (m->d_idx) cudaFree(m->d_idx);
   if (m->d_counters) cudaFree(m->d_counters);
+  if (m->d_render_lines) cudaFree(m->d_render_lines);
+  if (m->d_render_scene) cudaFree(m->d_render_scene);
+  if (m->d_render_c) cudaFree(m->d_render_c);
   if (m->stream) cudaStreamDestroy(m->stream);
   delete m;
   return UMRS_OK;
@@ -420,6 +427,67 @@ int umrs_scan_batch(umrs_map* m, const float* obj_segs_xyxy, int32_t n_obj,
   if (hit_idx_out)
     UMRS_CUDA(cudaMemcpyAsync(hit_idx_out, m->d_idx, sizeof(int32_t) * n_out,
                               cudaMemcpyDeviceToHost, m->stream));
+  UMRS_CUDA(cudaStreamSynchronize(m->stream));
+  return UMRS_OK;
+}
+
+// ---- opt-in reference render (tier A) ------------------------------------------------
+int umrs_scan_batch_reference_render_device(umrs_map* m, const float* obj_segs_dev, int32_t n_obj,
+                                            const float* fans_dev, int32_t n_fans, float range_max,
+                                            int32_t num_rays, float* ranges_dev, void* stream) {
+  if (m == NULL || n_fans < 0 || num_rays <= 0 || n_obj < 0 || ranges_dev == NULL ||
+      (n_fans > 0 && fans_dev == NULL) || (n_obj > 0 && obj_segs_dev == NULL))
+    return UMRS_ERR_INVALID;
+  if (n_fans == 0) return UMRS_OK;
+  if (m->d_render_lines == nullptr) {
+    const size_t n = (size_t)kRenderFansPerLaunch * 2000;
+    UMRS_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_render_lines), sizeof(float4) * n));
+    UMRS_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_render_scene), sizeof(float4) * n));
+    UMRS_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_render_c), sizeof(float) * n));
+  }
+  RenderScanParams p;
+  memset(&p, 0, sizeof(p));
+  p.segs = m->d_segs;
+  p.n_map = m->n;
+  p.obj_segs = reinterpret_cast<const float4*>(obj_segs_dev);
+  p.n_obj = n_obj;
+  p.fans = reinterpret_cast<const float4*>(fans_dev);
+  p.n_fans = n_fans;
+  p.range_max = range_max;
+  p.num_rays = num_rays;
+  p.ranges = ranges_dev;
+  p.scratch_lines = m->d_render_lines;
+  p.scratch_scene = m->d_render_scene;
+  p.scratch_c = m->d_render_c;
+  cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
+  for (int b = 0; b < n_fans; b += kRenderFansPerLaunch)   // stream order: one scratch, reused
+    UMRS_CUDA(launch_reference_render(p, b, b + kRenderFansPerLaunch < n_fans ? b + kRenderFansPerLaunch : n_fans, st));
+  return UMRS_OK;
+}
+
+int umrs_scan_batch_reference_render(umrs_map* m, const float* obj_segs_xyxy, int32_t n_obj,
+                                     const float* fans, int32_t n_fans, float range_max,
+                                     int32_t num_rays, float* ranges_out) {
+  if (m == NULL || n_fans < 0 || num_rays <= 0 || n_obj < 0 || ranges_out == NULL ||
+      (n_fans > 0 && fans == NULL) || (n_obj > 0 && obj_segs_xyxy == NULL))
+    return UMRS_ERR_INVALID;
+  if (n_fans == 0) return UMRS_OK;
+  const size_t n_out = (size_t)n_fans * (size_t)num_rays;
+  int st;
+  if ((st = grow(&m->d_fans, &m->fans_cap, (size_t)n_fans)) != UMRS_OK) return st;
+  if ((st = grow(&m->d_obj, &m->obj_cap, (size_t)(n_obj > 0 ? n_obj : 1))) != UMRS_OK) return st;
+  if ((st = grow(&m->d_ranges, &m->ranges_cap, n_out)) != UMRS_OK) return st;
+  UMRS_CUDA(cudaMemcpyAsync(m->d_fans, fans, sizeof(float4) * (size_t)n_fans,
+                            cudaMemcpyHostToDevice, m->stream));
+  if (n_obj > 0)
+    UMRS_CUDA(cudaMemcpyAsync(m->d_obj, obj_segs_xyxy, sizeof(float4) * (size_t)n_obj,
+                              cudaMemcpyHostToDevice, m->stream));
+  st = umrs_scan_batch_reference_render_device(m, reinterpret_cast<const float*>(m->d_obj), n_obj,
+                                               reinterpret_cast<const float*>(m->d_fans), n_fans,
+                                               range_max, num_rays, m->d_ranges, m->stream);
+  if (st != UMRS_OK) return st;
+  UMRS_CUDA(cudaMemcpyAsync(ranges_out, m->d_ranges, sizeof(float) * n_out,
+                            cudaMemcpyDeviceToHost, m->stream));
   UMRS_CUDA(cudaStreamSynchronize(m->stream));
   return UMRS_OK;
 }

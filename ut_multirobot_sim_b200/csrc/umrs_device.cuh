@@ -125,7 +125,7 @@ __device__ __forceinline__ bool near_a_ray(const Lattice& L, float a) {
 }
 
 // float(atan2(double)) of vector_map.cpp:449-450; out of line (rare path, large body).
-__device__ __noinline__ float atan2_ref(float y, float x) {
+static __device__ __noinline__ float atan2_ref(float y, float x) {
   return (float)atan2((double)y, (double)x);
 }
 

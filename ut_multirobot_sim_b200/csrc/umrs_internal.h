@@ -118,6 +118,26 @@ struct WorldStepParams {
   int32_t laser_noise, motion_noise;
 };
 
+// Opt-in reference render (umrs_render.cu): one warp per fan, scratch for the fans of ONE launch.
+struct RenderScanParams {
+  const float4* segs;      // cleaned map lines in MAP ORDER (GetSceneLines order)
+  int32_t n_map;
+  const float4* obj_segs;  // shared object lines (nullable)
+  int32_t n_obj;
+  const float4* fans;      // {loc_x, loc_y, angle_min, angle_max}
+  int32_t n_fans;
+  float range_max;
+  int32_t num_rays;
+  float* ranges;           // [n_fans][num_rays]
+  float4* scratch_lines;   // [fans per launch][2000] candidate list, then the cast constants
+  float4* scratch_scene;   // [fans per launch][2000]
+  float* scratch_c;        // [fans per launch][2000]
+  int32_t fan_first_scratch;
+};
+constexpr int kRenderFansPerLaunch = 2048;   // 147 MB of scratch
+cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, int fan_end,
+                                    cudaStream_t stream);
+
 // Dynamic shared memory of one fan CTA.
 size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent,
                        int multipass);
