@@ -66,6 +66,15 @@ class VectorMapT {
       flat_obj_[4 * i + 3] = object_lines[i].p1.y();
     }
     scan->resize(static_cast<size_t>(num_rays));
+    if (reference_render) {
+      // the reference's own SceneRender/TrimOcclusion pass on the GPU: its very bits
+      const float fan[4] = {loc.x(), loc.y(), angle_min, angle_max};
+      Check(umrs_scan_batch_reference_render(map_, flat_obj_.empty() ? nullptr : flat_obj_.data(),
+                                             static_cast<int32_t>(object_lines.size()), fan, 1, range_max,
+                                             num_rays, scan->data()),
+            "umrs_scan_batch_reference_render");
+      return;
+    }
     Check(umrs_predicted_scan(map_, flat_obj_.empty() ? nullptr : flat_obj_.data(),
                               static_cast<int32_t>(object_lines.size()), loc.x(), loc.y(), range_min,
                               range_max, angle_min, angle_max, num_rays, scan->data(), nullptr),
@@ -77,6 +86,9 @@ class VectorMapT {
   std::vector<Line> lines;         // vector_map.h:78 (read-only mirror of the device map)
   std::vector<Line> object_lines;  // vector_map.h:81
   std::string file_name;           // vector_map.h:79
+  // false (default): exact nearest hit per ray.  true: bit-identical to the reference's
+  // GetPredictedScan, occlusion-trimming defects included (slower: O(L^2) per scan).
+  bool reference_render = false;
 
  private:
   static void Check(int status, const char* where) {

@@ -124,7 +124,27 @@ def config4():
                       "passes_per_fan": cnt["passes"] / n_fans}))
 
 
+def reference_render():
+    """The opt-in reference render (bit-identical to the reference's GetPredictedScan), device buffers."""
+    for M in (256, 1024):
+        segs = umrs.map_cleanup(synth.floorplan_segments(M, extent=200.0, seed=1234))
+        vmap = umrs.VectorMap(lines=segs)
+        for W in (1, 64, 4096):
+            poses = synth.sample_free_poses_fast(segs, W, 200.0, seed=11)
+            fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - d135, poses[:, 2] + d135], 1).astype(np.float32)
+            d_fans = torch.from_numpy(fans).cuda()
+            d_out = torch.empty((W, 1081), dtype=torch.float32, device="cuda")
+            st = torch.cuda.Stream()
+
+            def run():
+                _lib.check(lib.umrs_scan_batch_reference_render_device(
+                    vmap._h, None, 0, d_fans.data_ptr(), W, 100.0, 1081, d_out.data_ptr(), st.cuda_stream), "render")
+            ms = ev_time(run, st, 5, warm=2)
+            print(json.dumps({"config": "reference_render", "map_segments": int(len(segs)), "fans": W,
+                              "ms_per_call": ms, "rays_per_s": W * 1081 / ms * 1e3}))
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["1", "2", "3", "4"]
+    which = sys.argv[1:] or ["1", "2", "3", "4", "R"]
     for c in which:
-        {"1": config1, "2": config2, "3": config3, "4": config4}[c]()
+        {"1": config1, "2": config2, "3": config3, "4": config4, "R": reference_render}[c]()
