@@ -70,56 +70,57 @@ UMRS_HD V2 ray_intersection(const Seg& s, V2 p, V2 dir) {
 // it is iterating, :174); the piece is then in *pushed.
 UMRS_HD bool trim_occlusion(V2 loc, const Seg& test, Seg* trim, Seg* pushed) {
   const float sqeps = 1e-8f;                      // :62
-  V2 l1_p0 = test.p0, l1_p1 = test.p1;            // :65-67
-  V2 l1_r0 = sub(l1_p0, loc), l1_r1 = sub(l1_p1, loc);
-  V2 l2_p0 = trim->p0, l2_p1 = trim->p1;          // :73-75
-  V2 l2_r0 = sub(l2_p0, loc), l2_r1 = sub(l2_p1, loc);
-  // r0 -> r1 in right-handed order, :82-89
-  if (cross2(l1_r0, l1_r1) < 0.0f) {
-    V2 t = l1_r0; l1_r0 = l1_r1; l1_r1 = t;
-    t = l1_p0; l1_p0 = l1_p1; l1_p1 = t;
+  // end points (ta, tb of `test`; ua, ub of `trim`) and the same relative to loc (ra, rb; sa, sb)
+  V2 ta = test.p0, tb = test.p1;                  // :65-67
+  V2 ra = sub(ta, loc), rb = sub(tb, loc);
+  V2 ua = trim->p0, ub = trim->p1;                // :73-75
+  V2 sa = sub(ua, loc), sb = sub(ub, loc);
+  // each pair in right-handed order as seen from loc, :82-89
+  if (cross2(ra, rb) < 0.0f) {
+    V2 t = ra; ra = rb; rb = t;
+    t = ta; ta = tb; tb = t;
   }
-  if (cross2(l2_r0, l2_r1) < 0.0f) {
-    V2 t = l2_r0; l2_r0 = l2_r1; l2_r1 = t;
-    t = l2_p0; l2_p0 = l2_p1; l2_p1 = t;
+  if (cross2(sa, sb) < 0.0f) {
+    V2 t = sa; sa = sb; sb = t;
+    t = ua; ua = ub; ub = t;
   }
   // no interaction, :98-105
-  if ((cross2(l1_r0, l2_r0) >= 0.0f && cross2(l1_r1, l2_r0) >= 0.0f) ||
-      (cross2(l2_r0, l1_r0) >= 0.0f && cross2(l2_r1, l1_r0) >= 0.0f)) {
+  if ((cross2(ra, sa) >= 0.0f && cross2(rb, sa) >= 0.0f) ||
+      (cross2(sa, ra) >= 0.0f && cross2(sb, ra) >= 0.0f)) {
     return false;
   }
-  const bool ray_occlusion0 = ray_intersects(*trim, loc, l1_r0);   // :109
-  const bool ray_occlusion1 = ray_intersects(*trim, loc, l1_r1);   // :112
-  const bool complete = intersects(test, loc, l2_p0) && intersects(test, loc, l2_p1);   // :121-122
+  const bool ray_occlusion0 = ray_intersects(*trim, loc, ra);   // :109
+  const bool ray_occlusion1 = ray_intersects(*trim, loc, rb);   // :112
+  const bool complete = intersects(test, loc, ua) && intersects(test, loc, ub);   // :121-122
   const bool occlusion0 = ray_occlusion0 &&                        // :125-127
-      (touches(*trim, loc) || touches(*trim, l1_p0) || !intersects(*trim, loc, l1_p0));
+      (touches(*trim, loc) || touches(*trim, ta) || !intersects(*trim, loc, ta));
   const bool occlusion1 = ray_occlusion1 &&                        // :130-132
-      (touches(*trim, loc) || touches(*trim, l1_p1) || !intersects(*trim, loc, l1_p1));
+      (touches(*trim, loc) || touches(*trim, tb) || !intersects(*trim, loc, tb));
   if (complete) {                                                  // :143-149
     const float z = (float)0.1;
     trim->p0.x = z; trim->p0.y = z; trim->p1.x = z; trim->p1.y = z;
     return false;
   }
   if (occlusion0 && occlusion1) {                                  // :150-170
-    const V2 right_end = ray_intersection(*trim, loc, l1_r0);
-    const V2 left_end = ray_intersection(*trim, loc, l1_r1);
-    trim->p0 = l2_p0;
+    const V2 right_end = ray_intersection(*trim, loc, ra);
+    const V2 left_end = ray_intersection(*trim, loc, rb);
+    trim->p0 = ua;
     trim->p1 = right_end;
-    if (sq_norm(sub(left_end, l2_p1)) > sqeps) {
+    if (sq_norm(sub(left_end, ub)) > sqeps) {
       pushed->p0 = left_end;
-      pushed->p1 = l2_p1;
+      pushed->p1 = ub;
       return true;
     }
     return false;
   }
   if (occlusion0) {                                                // :171-175
-    const V2 right_end = ray_intersection(*trim, loc, l1_r0);
-    trim->p0 = l2_p0;
+    const V2 right_end = ray_intersection(*trim, loc, ra);
+    trim->p0 = ua;
     trim->p1 = right_end;
   } else if (occlusion1) {                                         // :176-180
-    const V2 left_end = ray_intersection(*trim, loc, l1_r1);
+    const V2 left_end = ray_intersection(*trim, loc, rb);
     trim->p0 = left_end;
-    trim->p1 = l2_p1;
+    trim->p1 = ub;
   }
   return false;
 }
