@@ -439,11 +439,19 @@ int umrs_scan_batch_reference_render_device(umrs_map* m, const float* obj_segs_d
       (n_fans > 0 && fans_dev == NULL) || (n_obj > 0 && obj_segs_dev == NULL))
     return UMRS_ERR_INVALID;
   if (n_fans == 0) return UMRS_OK;
-  if (m->d_render_lines == nullptr) {
+  if (m->d_render_c == nullptr) {   // all three or none
     const size_t n = (size_t)kRenderFansPerLaunch * 2000;
-    UMRS_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_render_lines), sizeof(float4) * n));
-    UMRS_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_render_scene), sizeof(float4) * n));
-    UMRS_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_render_c), sizeof(float) * n));
+    float4 *a = nullptr, *b = nullptr;
+    float* c = nullptr;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&a), sizeof(float4) * n);
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&b), sizeof(float4) * n);
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&c), sizeof(float) * n);
+    if (e != cudaSuccess) {
+      if (a) cudaFree(a);
+      if (b) cudaFree(b);
+      return cuda_fail(e, "reference render scratch");
+    }
+    m->d_render_lines = a; m->d_render_scene = b; m->d_render_c = c;
   }
   RenderScanParams p;
   memset(&p, 0, sizeof(p));
