@@ -232,6 +232,9 @@ typedef struct umrs_world_desc {
   int32_t motion_noise_enabled;    /* 0: Ackermann angular error draws are 0 */
   int32_t world_index_base;        /* global index of world 0 (multi-GPU shards) */
   int32_t write_hit_idx;           /* keep the hit-segment index buffer */
+  int32_t reference_render;        /* 1: every scan goes through the reference's own render
+                                    * (see umrs_scan_batch_reference_render): the reference's bits,
+                                    * O(L^2) per scan, no hit indices */
 } umrs_world_desc;
 
 int umrs_world_create(umrs_map* map, const umrs_world_desc* desc, umrs_world** out);

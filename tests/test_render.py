@@ -122,3 +122,79 @@ def test_gpu_reference_render_argument_validation_and_empty_map():
     assert vmap.ScanBatchReferenceRender(np.zeros((0, 4), np.float32), 30.0, 16).shape == (0, 16)
     with pytest.raises(umrs._lib.UmrsError):
         vmap.ScanBatchReferenceRender(np.array([[0, 0, -1, 1]], np.float32), 30.0, 0)
+
+
+@pytest.mark.gpu
+def test_world_step_in_reference_render_mode_equals_the_reference_scan(ref):
+    """umrs_world_desc.reference_render: the fused tick (entity steps, footprints, laser origin)
+    followed by the reference's own render per robot.  Crowded worlds (8 robots of three kinds,
+    16 humans, 1 object): every scan of every step equals the unmodified reference
+    GetPredictedScan on the step's own fan and object lines (minus the robot's own body) to
+    the bit."""
+    import ut_multirobot_sim_b200 as umrs
+    extent = 60.0
+    segs = umrs.map_cleanup(synth.floorplan_segments(300, extent=extent, seed=1234))
+    vmap = umrs.VectorMap(lines=segs)
+    rps = [umrs.default_robot("ut_jackal") for _ in range(3)] + [umrs.default_robot("bwibot") for _ in range(3)] + \
+          [umrs.default_robot("cobot") for _ in range(2)]
+    hps = [umrs.default_human() for _ in range(16)]
+    W, R = 3, 8
+    world = umrs.World(vmap, rps, W, humans=hps, static_objects=1, seed=9, reference_render=True)
+    free = synth.sample_free_poses_fast(segs, W * R, extent, seed=21, clearance=0.6).reshape(W, R, 3)
+    hs = synth.sample_free_poses_fast(segs, W * 32, extent, seed=22).reshape(W, 32, 3)
+    st = synth.sample_free_poses_fast(segs, W, extent, seed=23).reshape(W, 1, 3)
+    for arr in (free, hs, st):
+        c = free[:, :1, :2]
+        arr[..., :2] = c + (arr[..., :2] - c) * 0.2
+    world.SetPose(free)
+    world.SetHumans(hs[:, :16], hs[:, 16:])
+    world.SetStaticObjects(st)
+    rm = ref.map_from_segments(segs, False)
+    rng = np.random.default_rng(0)
+    bodies = [k for k, q in enumerate(rps) if q.footprint_enabled]
+    checked = 0
+    for step in range(3):
+        ranges = world.Step(rng.uniform(-1, 1, (W, R, 3)).astype(np.float32))
+        lines, fp = world.GetLines(), world.fan_params()
+        for w in range(W):
+            for r, rp in enumerate(rps):
+                hdr = world.scan_header(r)
+                o = lines[w]
+                if rp.footprint_enabled:
+                    b0 = 4 + 20 * 16 + 4 * bodies.index(r)
+                    o = np.concatenate([o[:b0], o[b0 + 4:]])
+                rm.set_object_lines(o)
+                f = fp[w, r]
+                want = rm.predicted_scan(f[:2], 0.4, rp.laser.range_max, f[2], f[3], hdr.num_rays)
+                got = ranges[w, hdr.ranges_offset:hdr.ranges_offset + hdr.num_rays]
+                assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (step, w, r)
+                checked += hdr.num_rays
+    assert checked == 3 * W * world.rays_per_world
+    with pytest.raises(umrs._lib.UmrsError):      # the reference has no hit index
+        world.Step(np.zeros((W, R, 3), np.float32), want_idx=True)
+
+
+@pytest.mark.gpu
+def test_reference_render_worlds_draw_the_same_noise_as_default_worlds():
+    """Laser noise in reference-render worlds is the step kernel's Philox stream: wherever the
+    clean ranges of the two modes agree, the noisy outputs agree to the bit as well."""
+    import ut_multirobot_sim_b200 as umrs
+    segs = umrs.map_cleanup(synth.floorplan_segments(256, extent=100.0, seed=5))
+    vmap = umrs.VectorMap(lines=segs)
+    car = umrs.default_robot("ut_automata")
+    W = 64
+    poses = synth.sample_free_poses_fast(segs, W, 100.0, seed=11).reshape(W, 1, 3)
+    cmds = synth.ackermann_commands(W, 1, 0)
+    out = {}
+    for render in (False, True):
+        for noise in (False, True):
+            world = umrs.World(vmap, [car], W, seed=77, laser_noise=noise, reference_render=render,
+                               write_hit_idx=False)
+            world.SetPose(poses)
+            world.Step(cmds)
+            out[(render, noise)] = world.Step(cmds).copy()
+    same_clean = out[(False, False)].view(np.uint32) == out[(True, False)].view(np.uint32)
+    assert same_clean.mean() > 0.9      # bitwise: the trimmed-piece drift (class D6) counts as different
+    a, b = out[(False, True)], out[(True, True)]
+    assert np.array_equal(a.view(np.uint32)[same_clean], b.view(np.uint32)[same_clean])
+    assert (a != out[(False, False)]).mean() > 0.9      # the noise is on

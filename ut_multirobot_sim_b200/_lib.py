@@ -62,7 +62,8 @@ class WorldDesc(C.Structure):
                 ("robots", C.POINTER(RobotParams)), ("humans", C.POINTER(HumanParams)),
                 ("dt", C.c_float), ("seed", C.c_uint64),
                 ("laser_noise_enabled", C.c_int32), ("motion_noise_enabled", C.c_int32),
-                ("world_index_base", C.c_int32), ("write_hit_idx", C.c_int32)]
+                ("world_index_base", C.c_int32), ("write_hit_idx", C.c_int32),
+                ("reference_render", C.c_int32)]
 
 
 _P = C.c_void_p

@@ -172,7 +172,7 @@ class World:
 
     def __init__(self, vmap, robots, num_worlds, humans=(), static_objects=0, dt=0.025,
                  seed=0, laser_noise=False, motion_noise=False, world_index_base=0,
-                 write_hit_idx=True):
+                 write_hit_idx=True, reference_render=False):
         self._lib = _lib.load()
         self._map = vmap
         self.W, self.R, self.H, self.O = int(num_worlds), len(robots), len(humans), int(static_objects)
@@ -186,6 +186,7 @@ class World:
         d.dt, d.seed = dt, seed
         d.laser_noise_enabled, d.motion_noise_enabled = int(laser_noise), int(motion_noise)
         d.world_index_base, d.write_hit_idx = int(world_index_base), int(write_hit_idx)
+        d.reference_render = int(reference_render)
         self._h = C.c_void_p()
         check(self._lib.umrs_world_create(vmap._h, C.byref(d), C.byref(self._h)), "umrs_world_create")
         n = C.c_int32(0)

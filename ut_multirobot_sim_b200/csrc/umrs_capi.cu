@@ -82,6 +82,7 @@ void capi_set_error(const char* msg) { g_last_cuda_error = msg; }
 struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; int32_t multipass; };
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
+void capi_map_segments(const umrs_map* m, const float4** segs_map_order, int32_t* n);
 }  // namespace umrs
 
 // ================================== map ==========================================
@@ -205,6 +206,12 @@ static int map_from_clean(const float* segs, int32_t n, umrs_map** out) {
 }
 
 namespace umrs {
+// The cleaned map lines on the device in MAP ORDER (GetSceneLines order; the reference render).
+void capi_map_segments(const umrs_map* m, const float4** segs_map_order, int32_t* n) {
+  *segs_map_order = m->d_segs;
+  *n = m->n;
+}
+
 // Picks the kernel variant and the shared-memory plan for a launch against map m.
 //   K1 (kernel 0): every fan streams the whole map;  K2 (kernel 1): grid rows.
 // auto: K2 from 4096 map segments up.  cap = candidate slots per pass.

@@ -116,6 +116,7 @@ struct WorldStepParams {
   uint32_t step_lo, step_hi;
   int32_t world_base;
   int32_t laser_noise, motion_noise;
+  int32_t skip_scan;         // stop after the entity steps / object lines / fan (reference render follows)
 };
 
 // Opt-in reference render (umrs_render.cu): one warp per fan, scratch for the fans of ONE launch.
@@ -132,7 +133,21 @@ struct RenderScanParams {
   float4* scratch_lines;   // [fans per launch][2000] candidate list, then the cast constants
   float4* scratch_scene;   // [fans per launch][2000]
   float* scratch_c;        // [fans per launch][2000]
-  int32_t fan_first_scratch;
+  int32_t fan_begin;       // first fan of this launch (scratch slot = fan - fan_begin)
+  // world mode (world_R > 0): fan g = (world g / R, robot g % R) of a world step; fans = the
+  // step's fan_params, object lines per world minus the robot's own body, per-robot laser
+  int32_t world_R;
+  const float4* world_obj_lines;      // [W][L_obj]
+  int32_t L_obj;
+  const int32_t* ent_off;             // [entities + 1] first object line of entity e
+  int32_t first_robot_ent;
+  const umrs_robot_params* robots;    // [R]
+  const int32_t* ray_off;             // [R]
+  const int32_t* num_rays_r;          // [R]
+  int32_t rays_per_world;
+  int32_t laser_noise;
+  uint32_t key0, key1, step_lo, step_hi;
+  int32_t world_base;
 };
 constexpr int kRenderFansPerLaunch = 2048;   // 147 MB of scratch
 cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, int fan_end,

@@ -1000,6 +1000,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   if (t == 0 && p.fan_params != nullptr)
     p.fan_params[(size_t)w * p.R + r] = make_float4(fan.lx, fan.ly, fan.amin, fan.amax);
   __syncthreads();
+  if (p.skip_scan) return;   // reference-render worlds: the scan is k_scan_reference_render's
 
   const int skip_lo = p.ent_off[p.O + p.H + r], skip_hi = p.ent_off[p.O + p.H + r + 1];
   PostProcess post;

@@ -62,16 +62,35 @@ __device__ __forceinline__ void append_ordered(float4* lines, int& n_lines, bool
 __global__ void __launch_bounds__(32 * kRenderWarpsPerCta)
 k_scan_reference_render(const RenderScanParams p) {
   const int lane = threadIdx.x & 31;
-  const int f = (int)blockIdx.x * kRenderWarpsPerCta + (int)(threadIdx.x >> 5);
-  if (f >= p.n_fans) return;
-  const int slot = f - p.fan_first_scratch;   // scratch is sized for one launch
+  const int slot = (int)blockIdx.x * kRenderWarpsPerCta + (int)(threadIdx.x >> 5);
+  if (slot >= p.n_fans) return;
+  const int f = p.fan_begin + slot;           // scratch is sized for one launch
   float4* lines = p.scratch_lines + (size_t)slot * render::kRenderMaxLines;
   float4* scene = p.scratch_scene + (size_t)slot * render::kRenderMaxLines;
   float* cast_c = p.scratch_c + (size_t)slot * render::kRenderMaxLines;
-  const float4 fp = __ldg(p.fans + f);
+  const float4 fp = p.fans[f];
   V2 loc;
   loc.x = fp.x; loc.y = fp.y;
   const float amin = fp.z, amax = fp.w;
+  // batch mode: one shared object-line set, one laser.  World mode: the object lines of the
+  // fan's world minus the robot's own body, the robot's own laser (simulator.cpp:398-411).
+  float range_max = p.range_max;
+  int num_rays = p.num_rays;
+  const float4* obj = p.obj_segs;
+  int n_obj = p.n_obj, skip_lo = 0, skip_hi = 0;
+  float* out = p.ranges + (size_t)f * (size_t)p.num_rays;
+  int wr = 0, ww = 0;
+  if (p.world_R > 0) {
+    ww = f / p.world_R;
+    wr = f % p.world_R;
+    range_max = p.robots[wr].laser.range_max;
+    num_rays = p.num_rays_r[wr];
+    obj = p.world_obj_lines + (size_t)ww * (size_t)p.L_obj;
+    n_obj = p.L_obj;
+    skip_lo = p.ent_off[p.first_robot_ent + wr];
+    skip_hi = p.ent_off[p.first_robot_ent + wr + 1];
+    out = p.ranges + (size_t)ww * (size_t)p.rays_per_world + (size_t)p.ray_off[wr];
+  }
 
   // ---- GetSceneLines: map lines, then object lines, in order --------------------------
   int n_lines = 0;
@@ -79,14 +98,17 @@ k_scan_reference_render(const RenderScanParams p) {
     const int k = b + lane;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     bool keep = false;
-    if (k < p.n_map) { s = __ldg(p.segs + k); keep = aabb_keep(s, loc.x, loc.y, p.range_max); }
+    if (k < p.n_map) { s = __ldg(p.segs + k); keep = aabb_keep(s, loc.x, loc.y, range_max); }
     append_ordered(lines, n_lines, keep, s, lane);
   }
-  for (int b = 0; b < p.n_obj; b += 32) {
+  for (int b = 0; b < n_obj; b += 32) {
     const int k = b + lane;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     bool keep = false;
-    if (k < p.n_obj) { s = p.obj_segs[k]; keep = aabb_keep(s, loc.x, loc.y, p.range_max); }
+    if (k < n_obj && !(k >= skip_lo && k < skip_hi)) {
+      s = obj[k];
+      keep = aabb_keep(s, loc.x, loc.y, range_max);
+    }
     append_ordered(lines, n_lines, keep, s, lane);
   }
   __syncwarp();
@@ -147,7 +169,7 @@ k_scan_reference_render(const RenderScanParams p) {
   }
 
   // ---- LineCast list, :439-456 (ordered; the candidate list is free now and takes it) ----
-  const Lattice L = make_lattice(amin, amax, p.num_rays);
+  const Lattice L = make_lattice(amin, amax, num_rays);
   int n_cast = 0;
   for (int b = 0; b < n_scene; b += 32) {
     const int j = b + lane;
@@ -174,11 +196,15 @@ k_scan_reference_render(const RenderScanParams p) {
   }
   __syncwarp();
 
-  // ---- ray fill, :458-476: the FIRST cast that covers the ray -----------------------------
-  float* out = p.ranges + (size_t)f * (size_t)p.num_rays;
-  for (int i = lane; i < p.num_rays; i += 32) {
+  // ---- ray fill, :458-476: the FIRST cast that covers the ray; in world mode followed by
+  // publishLaser's dropout + noise (simulator.cpp:412-418) on the step kernel's Philox stream
+  // (ray i = 128 s + 32 q + l takes normal q of block 32 s + l, see finalise in umrs_kernels.cu)
+  const bool noisy = p.world_R > 0 && p.laser_noise != 0;
+  const float stddev = noisy ? p.robots[wr].laser.noise_stddev : 0.f;
+  const uint32_t fan_global = (uint32_t)(p.world_base + ww) * (uint32_t)(p.world_R > 0 ? p.world_R : 1) + (uint32_t)wr;
+  for (int i = lane; i < num_rays; i += 32) {
     const float a = ray_angle(L.amin, L.da, i);
-    float r = p.range_max;                                                   // :433
+    float r = range_max;                                                     // :433
     for (int c = 0; c < n_cast; ++c) {
       const float4 k = lines[c];
       if (cast_covers(k.x, k.y, a)) {                                        // :469-470
@@ -188,6 +214,16 @@ k_scan_reference_render(const RenderScanParams p) {
         break;
       }
     }
+    if (noisy) {
+      const uint32_t blk = (uint32_t)(((i >> 7) << 5) + (i & 31));
+      const uint4 w4 = philox4x32(make_uint4(blk, fan_global, p.step_lo, p.step_hi ^ kStreamLaser),
+                                  make_uint2(p.key0, p.key1));
+      const int q = (i >> 5) & 3;
+      const float2 g2 = (q < 2) ? box_muller(w4.x, w4.y) : box_muller(w4.z, w4.w);
+      const float g = (q & 1) ? g2.y : g2.x;
+      if ((double)r > (double)range_max - 0.1) r = 0.f;
+      else r = fmaxf(0.f, r + stddev * g);
+    }
     out[i] = r;
   }
 }
@@ -196,11 +232,8 @@ cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, in
                                     cudaStream_t stream) {
   if (fan_end <= fan_begin) return cudaSuccess;
   RenderScanParams q = p;
-  // the launch covers fans [fan_begin, fan_end): shift the per-fan pointers
-  q.fans = p.fans + fan_begin;
-  q.ranges = p.ranges + (size_t)fan_begin * (size_t)p.num_rays;
+  q.fan_begin = fan_begin;            // the launch covers fans [fan_begin, fan_end)
   q.n_fans = fan_end - fan_begin;
-  q.fan_first_scratch = 0;
   const int ctas = (q.n_fans + kRenderWarpsPerCta - 1) / kRenderWarpsPerCta;
   k_scan_reference_render<<<ctas, 32 * kRenderWarpsPerCta, 0, stream>>>(q);
   note_launch();

@@ -23,6 +23,7 @@ void capi_set_error(const char* msg);
 struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; int32_t multipass; };
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
+void capi_map_segments(const umrs_map* m, const float4** segs_map_order, int32_t* n);
 }  // namespace umrs
 
 #define UMRS_CUDA(call)                                          \
@@ -38,6 +39,8 @@ struct umrs_world {
   std::vector<umrs_robot_params> robots;
   std::vector<umrs_human_params> humans;
   ScanPlan plan;  // kernel variant + shared-memory plan, fixed at creation
+  const float4* map_segs_in_map_order = nullptr;   // for the reference render
+  int32_t n_map = 0;
   int32_t max_rays = 0;
   int32_t W = 0, R = 0, H = 0, O = 0;
   int32_t L_obj = 0, rays_per_world = 0;
@@ -66,6 +69,10 @@ struct umrs_world {
   float4* d_obj_lines = nullptr;
   float* d_pose = nullptr;
   unsigned long long* d_counters = nullptr;
+  // scratch of the reference render (desc.reference_render): kRenderFansPerLaunch fans
+  float4* d_render_lines = nullptr;
+  float4* d_render_scene = nullptr;
+  float* d_render_c = nullptr;
   bool counters_on = false;
   double* d_stats = nullptr;
 };
@@ -82,7 +89,8 @@ int umrs_world_destroy(umrs_world* w) {
   void* ptrs[] = {w->d_robots, w->d_humans, w->d_tmpl, w->d_line_ent, w->d_ent_off,
                   w->d_ray_off, w->d_num_rays, w->d_rs[0], w->d_rs[1], w->d_hs[0],
                   w->d_hs[1], w->d_static, w->d_cmds, w->d_mask, w->d_ranges, w->d_idx,
-                  w->d_fan_params, w->d_obj_lines, w->d_pose, w->d_counters, w->d_stats};
+                  w->d_fan_params, w->d_obj_lines, w->d_pose, w->d_counters, w->d_stats,
+                  w->d_render_lines, w->d_render_scene, w->d_render_c};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (w->stream) cudaStreamDestroy(w->stream);
@@ -109,6 +117,7 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (w->H > 0) w->humans.assign(d->humans, d->humans + w->H);
   w->desc.robots = nullptr;
   w->desc.humans = nullptr;
+  capi_map_segments(map, &w->map_segs_in_map_order, &w->n_map);
 
   // ---- object-line roster: [statics][humans][robot bodies] ---------------------
   std::vector<float> tmpl;      // xyxy per world-line
@@ -200,7 +209,10 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (ok()) e = dalloc(&w->d_cmds, WR * 3);
   if (ok()) e = dalloc(&w->d_mask, WR);
   if (ok()) e = dalloc(&w->d_ranges, n_rays);
-  if (ok() && d->write_hit_idx) e = dalloc(&w->d_idx, n_rays);
+  if (ok() && d->write_hit_idx && !d->reference_render) e = dalloc(&w->d_idx, n_rays);
+  if (ok() && d->reference_render) e = dalloc(&w->d_render_lines, (size_t)kRenderFansPerLaunch * 2000);
+  if (ok() && d->reference_render) e = dalloc(&w->d_render_scene, (size_t)kRenderFansPerLaunch * 2000);
+  if (ok() && d->reference_render) e = dalloc(&w->d_render_c, (size_t)kRenderFansPerLaunch * 2000);
   if (ok()) e = dalloc(&w->d_fan_params, WR);
   if (ok()) e = dalloc(&w->d_obj_lines, (size_t)w->W * w->L_obj);
   if (ok()) e = dalloc(&w->d_pose, WR * 3);
@@ -390,7 +402,36 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   p.motion_noise = w->desc.motion_noise_enabled;
   if (w->counters_on && first == 0)
     UMRS_CUDA(cudaMemsetAsync(w->d_counters, 0, sizeof(unsigned long long) * kNumCounters, stream));
+  p.skip_scan = w->desc.reference_render ? 1 : 0;
   UMRS_CUDA(launch_world_step(p, stream));
+  if (w->desc.reference_render) {
+    // the scans: the reference's own render over this launch's fans, on the fan parameters and
+    // object lines the step kernel has just written (stream order)
+    RenderScanParams q;
+    memset(&q, 0, sizeof(q));
+    q.segs = w->map_segs_in_map_order;
+    q.n_map = w->n_map;
+    q.fans = w->d_fan_params;
+    q.ranges = w->d_ranges;
+    q.scratch_lines = w->d_render_lines;
+    q.scratch_scene = w->d_render_scene;
+    q.scratch_c = w->d_render_c;
+    q.world_R = w->R;
+    q.world_obj_lines = w->d_obj_lines;
+    q.L_obj = w->L_obj;
+    q.ent_off = w->d_ent_off;
+    q.first_robot_ent = w->O + w->H;
+    q.robots = w->d_robots;
+    q.ray_off = w->d_ray_off;
+    q.num_rays_r = w->d_num_rays;
+    q.rays_per_world = w->rays_per_world;
+    q.laser_noise = w->desc.laser_noise_enabled;
+    q.key0 = p.key0; q.key1 = p.key1; q.step_lo = p.step_lo; q.step_hi = p.step_hi;
+    q.world_base = w->desc.world_index_base;
+    const int f0 = first * w->R, f1 = (first + count) * w->R;
+    for (int b = f0; b < f1; b += kRenderFansPerLaunch)
+      UMRS_CUDA(launch_reference_render(q, b, b + kRenderFansPerLaunch < f1 ? b + kRenderFansPerLaunch : f1, stream));
+  }
   if (last) {
     w->cur ^= 1;
     w->step += 1;
@@ -409,7 +450,7 @@ int umrs_world_step_device(umrs_world* w, const float* cmds_dev, const uint8_t* 
 int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
                     float* ranges_out, int32_t* hit_idx_out) {
   if (w == NULL) return UMRS_ERR_INVALID;
-  if (hit_idx_out != NULL && w->d_idx == NULL) return UMRS_ERR_INVALID;
+  if (hit_idx_out != NULL && w->d_idx == NULL) return UMRS_ERR_INVALID;   // also: reference-render worlds
   const size_t WR = (size_t)w->W * w->R;
   if (cmds)
     UMRS_CUDA(cudaMemcpyAsync(w->d_cmds, cmds, sizeof(float) * WR * 3, cudaMemcpyHostToDevice, w->stream));
