@@ -61,6 +61,19 @@ def _compare(oracle, refmap, segs, obj, fans, range_max, n, r_gpu, i_gpu, skip=N
     return row
 
 
+def _render_identical(vmap, refmap, fans, range_max, n, obj=None):
+    """Fraction of rays on which the opt-in reference render equals the reference's output bitwise."""
+    if refmap is None:
+        return None
+    vmap.object_lines = np.zeros((0, 4), np.float32) if obj is None else obj
+    got = vmap.ScanBatchReferenceRender(fans, range_max, n)
+    refmap.set_object_lines(np.zeros((0, 4), np.float32) if obj is None else obj)
+    want = np.stack([refmap.predicted_scan(f[:2], 0.4, range_max, f[2], f[3], n) for f in fans])
+    frac = float((got.view(np.uint32) == want.view(np.uint32)).mean())
+    assert frac == 1.0
+    return frac
+
+
 def _ref_or_none():
     from tests import oracle_lib
     return oracle_lib.load_ref()
@@ -78,6 +91,7 @@ def test_config1_single_car_on_the_campus_map(oracle):
     ref = _ref_or_none()
     refmap = None if ref is None else ref.map_from_segments(segs, False)
     REPORT["config1"] = _compare(oracle, refmap, segs, None, fans, 100.0, 1081, r, i)
+    REPORT["config1"]["reference_render_bit_identical_to_reference"] = _render_identical(vmap, refmap, fans, 100.0, 1081)
 
 
 def test_config2_crowded_world(oracle):
@@ -162,6 +176,8 @@ def test_config3_batched_worlds(oracle, M):
         for k in ("within_1e-5_of_reference", "tier_b_within_1e-5_of_reference"):
             agg[k] = sum(r[k] * r["rays"] for r in rows) / tot
         agg["rays_only_the_gpu_gets_differently"] = sum(r["rays_only_the_gpu_gets_differently"] for r in rows)
+    agg["reference_render_bit_identical_to_reference"] = _render_identical(
+        vmap, refmap, fp[pick, 0], car.laser.range_max, 1081)
     REPORT["config3_M%d" % M] = agg
 
 
