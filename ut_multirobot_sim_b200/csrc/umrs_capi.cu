@@ -108,6 +108,9 @@ struct umrs_map {
   // work accounting of the scan entry points (umrs_map_enable_counters)
   unsigned long long* d_counters = nullptr;
   bool counters_on = false;
+  // pinned staging for small host-buffer scans (a pageable cudaMemcpyAsync stages and
+  // synchronises inside the driver; a single LaserScan is 4 KB)
+  float* h_stage = nullptr;        // [kStageFloats] outputs, then kStageIn floats of inputs
   // scratch of the opt-in reference render (allocated on first use)
   float4* d_render_lines = nullptr;
   float4* d_render_scene = nullptr;
@@ -321,6 +324,7 @@ int umrs_map_destroy(umrs_map* m) {
   if (m->d_ranges) cudaFree(m->d_ranges);
   if (m->d_idx) cudaFree(m->d_idx);
   if (m->d_counters) cudaFree(m->d_counters);
+  if (m->h_stage) cudaFreeHost(m->h_stage);
   if (m->d_render_lines) cudaFree(m->d_render_lines);
   if (m->d_render_scene) cudaFree(m->d_render_scene);
   if (m->d_render_c) cudaFree(m->d_render_c);
@@ -348,6 +352,9 @@ int umrs_map_set_scan_kernel(umrs_map* m, int32_t force) {
 }
 
 // ================================== scans =========================================
+static constexpr size_t kStageFloats = 64 * 1024;   // outputs staged through pinned memory up to 256 KB
+static constexpr size_t kStageIn = 16 * 1024;       // inputs (fans + object lines) up to 64 KB
+
 int umrs_map_enable_counters(umrs_map* m, int32_t on) {
   if (m == NULL) return UMRS_ERR_INVALID;
   if (on && m->d_counters == nullptr) {
@@ -419,22 +426,50 @@ int umrs_scan_batch(umrs_map* m, const float* obj_segs_xyxy, int32_t n_obj,
   if ((st = grow(&m->d_obj, &m->obj_cap, (size_t)(n_obj > 0 ? n_obj : 1))) != UMRS_OK) return st;
   if ((st = grow(&m->d_ranges, &m->ranges_cap, n_out)) != UMRS_OK) return st;
   if (hit_idx_out && (st = grow(&m->d_idx, &m->idx_cap, n_out)) != UMRS_OK) return st;
-  UMRS_CUDA(cudaMemcpyAsync(m->d_fans, fans, sizeof(float4) * (size_t)n_fans,
+  // Small calls (one LaserScan is 4 KB) go through pinned staging: every copy is then truly
+  // asynchronous and the call has ONE synchronisation point.
+  const size_t n_in = 4 * ((size_t)n_fans + (size_t)n_obj);
+  const size_t n_stage_out = n_out * (hit_idx_out ? 2 : 1);
+  const bool staged = n_in <= kStageIn && n_stage_out <= kStageFloats;
+  if (staged && m->h_stage == nullptr) {
+    if (cudaHostAlloc(reinterpret_cast<void**>(&m->h_stage), sizeof(float) * (kStageFloats + kStageIn),
+                      cudaHostAllocDefault) != cudaSuccess) {
+      cudaGetLastError();
+      m->h_stage = nullptr;
+    }
+  }
+  const bool use_stage = staged && m->h_stage != nullptr;
+  const float* src_fans = fans;
+  const float* src_obj = obj_segs_xyxy;
+  if (use_stage) {
+    float* in = m->h_stage + kStageFloats;
+    memcpy(in, fans, sizeof(float) * 4 * (size_t)n_fans);
+    if (n_obj > 0) memcpy(in + 4 * (size_t)n_fans, obj_segs_xyxy, sizeof(float) * 4 * (size_t)n_obj);
+    src_fans = in;
+    src_obj = in + 4 * (size_t)n_fans;
+  }
+  UMRS_CUDA(cudaMemcpyAsync(m->d_fans, src_fans, sizeof(float4) * (size_t)n_fans,
                             cudaMemcpyHostToDevice, m->stream));
   if (n_obj > 0)
-    UMRS_CUDA(cudaMemcpyAsync(m->d_obj, obj_segs_xyxy, sizeof(float4) * (size_t)n_obj,
+    UMRS_CUDA(cudaMemcpyAsync(m->d_obj, src_obj, sizeof(float4) * (size_t)n_obj,
                               cudaMemcpyHostToDevice, m->stream));
   st = umrs_scan_batch_device(m, reinterpret_cast<const float*>(m->d_obj), n_obj,
                               reinterpret_cast<const float*>(m->d_fans), n_fans, range_max,
                               num_rays, m->d_ranges, hit_idx_out ? m->d_idx : nullptr,
                               m->stream);
   if (st != UMRS_OK) return st;
-  UMRS_CUDA(cudaMemcpyAsync(ranges_out, m->d_ranges, sizeof(float) * n_out,
+  float* dst_r = use_stage ? m->h_stage : ranges_out;
+  int32_t* dst_i = use_stage ? reinterpret_cast<int32_t*>(m->h_stage + n_out) : hit_idx_out;
+  UMRS_CUDA(cudaMemcpyAsync(dst_r, m->d_ranges, sizeof(float) * n_out,
                             cudaMemcpyDeviceToHost, m->stream));
   if (hit_idx_out)
-    UMRS_CUDA(cudaMemcpyAsync(hit_idx_out, m->d_idx, sizeof(int32_t) * n_out,
+    UMRS_CUDA(cudaMemcpyAsync(dst_i, m->d_idx, sizeof(int32_t) * n_out,
                               cudaMemcpyDeviceToHost, m->stream));
   UMRS_CUDA(cudaStreamSynchronize(m->stream));
+  if (use_stage) {
+    memcpy(ranges_out, dst_r, sizeof(float) * n_out);
+    if (hit_idx_out) memcpy(hit_idx_out, dst_i, sizeof(int32_t) * n_out);
+  }
   return UMRS_OK;
 }
 
