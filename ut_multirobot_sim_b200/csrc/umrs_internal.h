@@ -149,7 +149,7 @@ struct RenderScanParams {
   uint32_t key0, key1, step_lo, step_hi;
   int32_t world_base;
 };
-constexpr int kRenderFansPerLaunch = 2048;   // 147 MB of scratch
+constexpr int kRenderFansPerLaunch = 4096;   // 295 MB of scratch; ~1.15 resident waves of warps on 148 SMs
 cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, int fan_end,
                                     cudaStream_t stream);
 
