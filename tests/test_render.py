@@ -198,3 +198,21 @@ def test_reference_render_worlds_draw_the_same_noise_as_default_worlds():
     a, b = out[(False, True)], out[(True, True)]
     assert np.array_equal(a.view(np.uint32)[same_clean], b.view(np.uint32)[same_clean])
     assert (a != out[(False, False)]).mean() > 0.9      # the noise is on
+
+
+@pytest.mark.gpu
+def test_gpu_reference_render_warp_per_fan_and_cta_per_fan_forms_agree(ref):
+    """Big batches take the warp-per-fan kernel, small ones the CTA-per-fan kernel: same bits,
+    and the reference's on a sample."""
+    import ut_multirobot_sim_b200 as umrs
+    segs, extent = _maps()["floorplan_300"]
+    vmap = umrs.VectorMap(lines=segs)
+    rm = ref.map_from_segments(segs, False)
+    poses = synth.sample_free_poses_fast(segs, 2000, extent, seed=13)
+    fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - D135, poses[:, 2] + D135], 1).astype(np.float32)
+    big = vmap.ScanBatchReferenceRender(fans, 100.0, 1081)                        # 2000 fans: warp per fan
+    small = np.concatenate([vmap.ScanBatchReferenceRender(fans[k:k + 500], 100.0, 1081)
+                            for k in range(0, 2000, 500)])                        # 500 fans: CTA per fan
+    assert np.array_equal(big.view(np.uint32), small.view(np.uint32))
+    want = rm.scan_batch(fans[::50], 0.4, 100.0, 1081, threads=4)
+    assert np.array_equal(big[::50].view(np.uint32), want.view(np.uint32))

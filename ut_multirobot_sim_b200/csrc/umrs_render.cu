@@ -4,8 +4,9 @@
 // the output is bit-identical to the reference's, occlusion-trimming defects included
 // (SURVEY.md 8c tier A).  The default scan (umrs_kernels.cu) is the exact nearest hit instead.
 //
-// One WARP per fan.  The render is sequential by nature (every candidate is trimmed by the
-// scene built so far, pieces split off are appended to the list being iterated), so the warp
+// One warp per fan for big batches, one 4-warp CTA per fan for small ones (a third of the
+// latency).  The render is sequential by nature (every candidate is trimmed by the
+// scene built so far, pieces split off are appended to the list being iterated), so the group
 // reproduces the reference's order of events:
 //   * trimming the current line by the scene (:231-234) changes the line, so the 32 lanes test
 //     32 consecutive scene entries against the CURRENT line, the lowest lane whose entry
@@ -25,6 +26,7 @@ using render::Seg;
 using render::V2;
 
 constexpr int kRenderWarpsPerCta = 4;
+constexpr int kRenderCtaPerFanUpTo = 148 * 6;   // one resident wave of 128-thread CTAs (80 registers)
 
 __device__ __forceinline__ Seg load_seg(const float4* p) {
   const float4 v = *p;
@@ -48,21 +50,72 @@ __device__ __forceinline__ bool same_bits(const Seg& a, const Seg& b) {
          __float_as_uint(a.p1.x) == __float_as_uint(b.p1.x) && __float_as_uint(a.p1.y) == __float_as_uint(b.p1.y);
 }
 
-// Ordered append of the lanes' candidates (GetSceneLines, vector_map.cpp:199-214).
-__device__ __forceinline__ void append_ordered(float4* lines, int& n_lines, bool keep, const float4& s,
-                                               int lane) {
-  const unsigned m = __ballot_sync(0xffffffffu, keep);
-  if (keep) {
-    const int pos = n_lines + __popc(m & ((1u << lane) - 1u));
-    if (pos < render::kRenderMaxLines) lines[pos] = s;
-  }
-  n_lines += __popc(m);
+// A fan is rendered by a GROUP of kW warps of a 4-warp CTA: kW = 1 (four fans per CTA: best
+// throughput for big batches) or kW = 4 (one fan per CTA: a third of the latency for a single
+// scan or a small batch).  The helpers below are the group-wide forms of ballot / prefix.
+struct GroupShared {
+  int first[4];     // per warp: lowest acting lane (32: none)
+  int count[4];     // per warp: lanes that append
+  float4 seg;       // the line a group adopts after an acting entry
+  int flag;
+};
+
+template <int kW>
+__device__ __forceinline__ void group_sync() {
+  if (kW == 1) __syncwarp(); else __syncthreads();
 }
 
+// Ordered append: group thread order (GetSceneLines :199-214, the pieces of :174, the casts).
+// Returns this thread's position; *total = entries appended by the group.
+template <int kW>
+__device__ __forceinline__ int group_append_pos(GroupShared* gs, bool keep, int base, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned m = __ballot_sync(0xffffffffu, keep);
+  int before = __popc(m & ((1u << lane) - 1u));
+  if (kW == 1) {
+    *total = __popc(m);
+    return base + before;
+  }
+  if (lane == 0) gs->count[warp] = __popc(m);
+  __syncthreads();
+  int t = 0;
+  for (int w = 0; w < kW; ++w) {
+    const int c = gs->count[w];
+    if (w < warp) before += c;
+    t += c;
+  }
+  __syncthreads();          // count[] is reused by the next call
+  *total = t;
+  return base + before;
+}
+
+// Lowest group thread whose `acts` is set (-1: none).
+template <int kW>
+__device__ __forceinline__ int group_first(GroupShared* gs, bool acts) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned m = __ballot_sync(0xffffffffu, acts);
+  if (kW == 1) return m ? __ffs(m) - 1 : -1;
+  if (lane == 0) gs->first[warp] = m ? __ffs(m) - 1 : 32;
+  __syncthreads();
+  int r = -1;
+  for (int w = kW - 1; w >= 0; --w) {
+    const int f = gs->first[w];
+    if (f < 32) r = w * 32 + f;
+  }
+  __syncthreads();
+  return r;
+}
+
+template <int kW>
 __global__ void __launch_bounds__(32 * kRenderWarpsPerCta)
 k_scan_reference_render(const RenderScanParams p) {
-  const int lane = threadIdx.x & 31;
-  const int slot = (int)blockIdx.x * kRenderWarpsPerCta + (int)(threadIdx.x >> 5);
+  __shared__ GroupShared gs_all[kRenderWarpsPerCta / kW];
+  constexpr int kGroup = 32 * kW;                        // threads per fan
+  const int gt = (int)threadIdx.x % kGroup;              // thread index inside the group
+  const int slot = (int)blockIdx.x * (kRenderWarpsPerCta / kW) + (int)threadIdx.x / kGroup;
+  GroupShared* gs = gs_all + (int)threadIdx.x / kGroup;
+  // (kW == 4: the whole CTA is one group and takes the __syncthreads below together;
+  //  kW == 1: no CTA-wide barrier is ever used, so a warp may leave early)
   if (slot >= p.n_fans) return;
   const int f = p.fan_begin + slot;           // scratch is sized for one launch
   float4* lines = p.scratch_lines + (size_t)slot * render::kRenderMaxLines;
@@ -94,24 +147,27 @@ k_scan_reference_render(const RenderScanParams p) {
 
   // ---- GetSceneLines: map lines, then object lines, in order --------------------------
   int n_lines = 0;
-  for (int b = 0; b < p.n_map; b += 32) {
-    const int k = b + lane;
+  for (int b = 0; b < p.n_map + n_obj; b += kGroup) {
+    // one index space: [map | objects]; a trip may straddle the boundary, order is kept
+    const int k = b + gt;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     bool keep = false;
-    if (k < p.n_map) { s = __ldg(p.segs + k); keep = aabb_keep(s, loc.x, loc.y, range_max); }
-    append_ordered(lines, n_lines, keep, s, lane);
-  }
-  for (int b = 0; b < n_obj; b += 32) {
-    const int k = b + lane;
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    bool keep = false;
-    if (k < n_obj && !(k >= skip_lo && k < skip_hi)) {
-      s = obj[k];
+    if (k < p.n_map) {
+      s = __ldg(p.segs + k);
       keep = aabb_keep(s, loc.x, loc.y, range_max);
+    } else if (k - p.n_map < n_obj) {
+      const int o = k - p.n_map;
+      if (!(o >= skip_lo && o < skip_hi)) {
+        s = obj[o];
+        keep = aabb_keep(s, loc.x, loc.y, range_max);
+      }
     }
-    append_ordered(lines, n_lines, keep, s, lane);
+    int total;
+    const int pos = group_append_pos<kW>(gs, keep, n_lines, &total);
+    if (keep && pos < render::kRenderMaxLines) lines[pos] = s;
+    n_lines += total;
   }
-  __syncwarp();
+  group_sync<kW>();
 
   // ---- SceneRender, vector_map.cpp:226-246 ---------------------------------------------
   int n_scene = 0;
@@ -119,7 +175,7 @@ k_scan_reference_render(const RenderScanParams p) {
     Seg cur = load_seg(lines + i);
     int j0 = 0;
     while (j0 < n_scene && render::sq_length(cur) >= render::kRenderEps) {   // :231
-      const int j = j0 + lane;
+      const int j = j0 + gt;
       Seg mine = cur, piece;
       piece.p0.x = piece.p0.y = piece.p1.x = piece.p1.y = 0.f;
       bool pushed = false, acts = false;
@@ -130,21 +186,33 @@ k_scan_reference_render(const RenderScanParams p) {
           acts = pushed || !same_bits(mine, cur);
         }
       }
-      const unsigned m = __ballot_sync(0xffffffffu, acts);
-      if (m == 0u) { j0 += 32; continue; }
-      const int first = __ffs(m) - 1;
-      cur = shfl_seg(mine, first);
-      const bool first_pushed = __shfl_sync(0xffffffffu, pushed ? 1 : 0, first) != 0;
-      if (first_pushed) {
-        if (lane == first && n_lines < render::kRenderMaxLines) store_seg(lines + n_lines, piece);
-        ++n_lines;
+      const int first = group_first<kW>(gs, acts);
+      if (first < 0) { j0 += kGroup; continue; }
+      // the lowest acting entry is what the reference's loop meets first: adopt its result
+      if (kW == 1) {
+        cur = shfl_seg(mine, first);
+        const bool fp_ = __shfl_sync(0xffffffffu, pushed ? 1 : 0, first) != 0;
+        if (fp_) {
+          if (gt == first && n_lines < render::kRenderMaxLines) store_seg(lines + n_lines, piece);
+          ++n_lines;
+        }
+      } else {
+        if (gt == first) {
+          gs->seg = make_float4(mine.p0.x, mine.p0.y, mine.p1.x, mine.p1.y);
+          gs->flag = pushed ? 1 : 0;
+          if (pushed && n_lines < render::kRenderMaxLines) store_seg(lines + n_lines, piece);
+        }
+        __syncthreads();
+        cur = load_seg(&gs->seg);
+        if (gs->flag) ++n_lines;
+        __syncthreads();
       }
       j0 += first + 1;
     }
-    __syncwarp();
+    group_sync<kW>();
     if (render::sq_length(cur) > render::kRenderEps) {                       // :236
-      for (int b = 0; b < n_scene; b += 32) {
-        const int j = b + lane;
+      for (int b = 0; b < n_scene; b += kGroup) {
+        const int j = b + gt;
         Seg piece;
         piece.p0.x = piece.p0.y = piece.p1.x = piece.p1.y = 0.f;
         bool pushed = false;
@@ -155,24 +223,22 @@ k_scan_reference_render(const RenderScanParams p) {
             store_seg(scene + j, t);
           }
         }
-        const unsigned m = __ballot_sync(0xffffffffu, pushed);
-        if (pushed) {
-          const int pos = n_lines + __popc(m & ((1u << lane) - 1u));
-          if (pos < render::kRenderMaxLines) store_seg(lines + pos, piece);
-        }
-        n_lines += __popc(m);
+        int total;
+        const int pos = group_append_pos<kW>(gs, pushed, n_lines, &total);
+        if (pushed && pos < render::kRenderMaxLines) store_seg(lines + pos, piece);
+        n_lines += total;
       }
-      if (lane == 0) store_seg(scene + n_scene, cur);
+      if (gt == 0) store_seg(scene + n_scene, cur);
       ++n_scene;
     }
-    __syncwarp();
+    group_sync<kW>();
   }
 
   // ---- LineCast list, :439-456 (ordered; the candidate list is free now and takes it) ----
   const Lattice L = make_lattice(amin, amax, num_rays);
   int n_cast = 0;
-  for (int b = 0; b < n_scene; b += 32) {
-    const int j = b + lane;
+  for (int b = 0; b < n_scene; b += kGroup) {
+    const int j = b + gt;
     bool keep = false;
     SegCast k;
     k.a0 = k.a1 = k.nx = k.ny = k.c = k.arc = 0.f;
@@ -186,15 +252,15 @@ k_scan_reference_render(const RenderScanParams p) {
         keep = k.valid;                                                      // :447
       }
     }
-    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    int total;
+    const int pos = group_append_pos<kW>(gs, keep, n_cast, &total);
     if (keep) {
-      const int pos = n_cast + __popc(m & ((1u << lane) - 1u));
       lines[pos] = make_float4(k.a0, k.a1, k.nx, k.ny);
       cast_c[pos] = k.c;
     }
-    n_cast += __popc(m);
+    n_cast += total;
   }
-  __syncwarp();
+  group_sync<kW>();
 
   // ---- ray fill, :458-476: the FIRST cast that covers the ray; in world mode followed by
   // publishLaser's dropout + noise (simulator.cpp:412-418) on the step kernel's Philox stream
@@ -202,7 +268,7 @@ k_scan_reference_render(const RenderScanParams p) {
   const bool noisy = p.world_R > 0 && p.laser_noise != 0;
   const float stddev = noisy ? p.robots[wr].laser.noise_stddev : 0.f;
   const uint32_t fan_global = (uint32_t)(p.world_base + ww) * (uint32_t)(p.world_R > 0 ? p.world_R : 1) + (uint32_t)wr;
-  for (int i = lane; i < num_rays; i += 32) {
+  for (int i = gt; i < num_rays; i += kGroup) {
     const float a = ray_angle(L.amin, L.da, i);
     float r = range_max;                                                     // :433
     for (int c = 0; c < n_cast; ++c) {
@@ -234,8 +300,13 @@ cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, in
   RenderScanParams q = p;
   q.fan_begin = fan_begin;            // the launch covers fans [fan_begin, fan_end)
   q.n_fans = fan_end - fan_begin;
-  const int ctas = (q.n_fans + kRenderWarpsPerCta - 1) / kRenderWarpsPerCta;
-  k_scan_reference_render<<<ctas, 32 * kRenderWarpsPerCta, 0, stream>>>(q);
+  // few fans: a whole CTA per fan (latency); many: a warp per fan (throughput)
+  if (q.n_fans <= kRenderCtaPerFanUpTo) {
+    k_scan_reference_render<kRenderWarpsPerCta><<<q.n_fans, 32 * kRenderWarpsPerCta, 0, stream>>>(q);
+  } else {
+    const int ctas = (q.n_fans + kRenderWarpsPerCta - 1) / kRenderWarpsPerCta;
+    k_scan_reference_render<1><<<ctas, 32 * kRenderWarpsPerCta, 0, stream>>>(q);
+  }
   note_launch();
   return cudaGetLastError();
 }
