@@ -386,3 +386,36 @@ def test_cleanup_reports_inputs_the_reference_never_finishes():
     for alg in (1, 2):
         with pytest.raises(_lib.UmrsError):
             umrs.map_cleanup(far, algorithm=alg)
+
+
+def test_grid_cleanup_property_random_lattice_maps(ref):
+    """Property check of SURVEY 8f-3 on 300 random maps whose end points sit on a coarse lattice
+    (so T-junctions, shared end points, collinear overlaps and duplicates are the norm, not the
+    exception): grid search == quadratic search == the compiled reference's Cleanup, bit for bit,
+    whenever the reference's loop terminates (the queue cap reports the others identically)."""
+    import ut_multirobot_sim_b200 as umrs
+    from ut_multirobot_sim_b200 import _lib
+    rng = np.random.default_rng(2024)
+    done = failed = 0
+    for trial in range(300):
+        n = int(rng.integers(1, 60))
+        step = float(rng.choice([0.25, 0.5, 1.0, 2.5]))
+        raw = (rng.integers(-12, 13, (n, 4)) * step).astype(np.float32)
+        if trial % 3 == 0:       # off-lattice perturbation of some end points
+            raw += (rng.random((n, 4)) < 0.3) * rng.normal(0, 0.01, (n, 4)).astype(np.float32)
+        out = []
+        for alg in (1, 2):
+            try:
+                out.append(umrs.map_cleanup(raw, algorithm=alg))
+            except _lib.UmrsError:
+                out.append(None)
+        assert (out[0] is None) == (out[1] is None), trial
+        if out[0] is None:
+            failed += 1
+            continue
+        assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32)), trial
+        if ref is not None:
+            r = np.asarray(ref.map_from_segments(raw, True).lines, np.float32)
+            assert np.array_equal(r.view(np.uint32), out[1].view(np.uint32)), trial
+        done += 1
+    assert done >= 250, (done, failed)
