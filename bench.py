@@ -282,27 +282,41 @@ def run_b200(args):
         ms = sum(a.elapsed_time(b) for a, b in zip(ev0, ev1))
         return ms, l1 - l0
 
-    def e2e_leg():
-        # host buffers (pinned), through the public host-buffer C-ABI call
+    def e2e_leg(pipelined):
+        # host buffers (pinned), through the public host-buffer C-ABI calls.  pipelined: successive
+        # ticks through umrs_world_step_async into two output buffers in turn, the previous tick's
+        # output waited for (and read) while the next one runs; else one synchronous call per tick.
         h_cmds = [torch.from_numpy(c).pin_memory() for c in cmd_sets]
-        h_ranges = torch.empty((W, N_RAYS), dtype=torch.float32).pin_memory()
+        h_out = [torch.empty((W, N_RAYS), dtype=torch.float32).pin_memory() for _ in range(2)]
         for s in range(min(Wm, 3)):
-            world.step_raw(h_cmds[s % 8].data_ptr(), None, h_ranges.data_ptr(), None)
+            world.step_raw(h_cmds[s % 8].data_ptr(), None, h_out[0].data_ptr(), None)
         barrier()
+        chk = 0.0
         t0 = time.perf_counter()
-        for s in range(K):
-            world.step_raw(h_cmds[s % 8].data_ptr(), None, h_ranges.data_ptr(), None)
+        if pipelined:
+            for s in range(K):
+                world.step_async_raw(h_cmds[s % 8].data_ptr(), None, h_out[s & 1].data_ptr(), None)
+                if s >= 1:
+                    world.wait_outputs(1)
+                    chk += float(h_out[(s - 1) & 1][0, 0])      # the step's result is read on the host
+            world.wait()
+            chk += float(h_out[(K - 1) & 1][0, 0])
+        else:
+            for s in range(K):
+                world.step_raw(h_cmds[s % 8].data_ptr(), None, h_out[0].data_ptr(), None)
+                chk += float(h_out[0][0, 0])
         barrier()
         dt = time.perf_counter() - t0
-        chk = float(h_ranges[0, :8].sum())
-        return dt * 1e3, h_cmds[0].numel() * 4, h_ranges.numel() * 4, chk
+        return dt * 1e3, h_cmds[0].numel() * 4, h_out[0].numel() * 4, chk
 
     sampler = ClockSampler(local_rank)
     sampler.start()
     ms_dev, launches = device_leg()
     clocks = sampler.result()
     ms_dev = max_over_ranks(ms_dev)
-    ms_e2e, h2d, d2h, _ = e2e_leg()
+    ms_sync, h2d, d2h, _ = e2e_leg(False)
+    ms_sync = max_over_ranks(ms_sync)
+    ms_e2e, h2d, d2h, _ = e2e_leg(True)
     ms_e2e = max_over_ranks(ms_e2e)
 
     # work accounting for the roofline: one untimed step with device counters on
@@ -353,7 +367,10 @@ def run_b200(args):
         "env_steps_per_sec": W * world_size * K / (ms_dev * 1e-3),
         "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": h2d * world_size,
                 "d2h_bytes_per_step": d2h * world_size, "ms_per_step": ms_e2e / K,
-                "env_steps_per_sec": W * world_size * K / (ms_e2e * 1e-3)},
+                "env_steps_per_sec": W * world_size * K / (ms_e2e * 1e-3),
+                "call": "umrs_world_step_async + umrs_world_wait_outputs (ticks pipelined, two pinned output buffers)",
+                "synchronous": {"value": total_rays * K / (ms_sync * 1e-3), "ms_per_step": ms_sync / K,
+                                "call": "umrs_world_step"}},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": FP32_PEAK_TFLOPS,

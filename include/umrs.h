@@ -272,6 +272,16 @@ int umrs_world_get_object_lines(umrs_world* world, float* segs_xyxy);
  * Host version copies cmds in and ranges (and idx, if non-NULL) out, synchronous. */
 int umrs_world_step(umrs_world* world, const float* cmds, const uint8_t* cmd_mask,
                     float* ranges_out, int32_t* hit_idx_out);
+/* The same tick, enqueued and not waited for: successive calls pipeline -- the device->host
+ * copy of tick k runs while tick k+1 computes -- so a host shell can publish scan k while
+ * the GPU works on k+1.  The caller's buffers belong to the library until waited for: use
+ * (at least) two output buffers in turn; pinned memory keeps the copies asynchronous.
+ * umrs_world_wait_outputs(w, back): blocks until the outputs of the tick issued `back`
+ * async calls ago (0 = the latest, at most 2) are in host memory.  umrs_world_wait: all of it. */
+int umrs_world_step_async(umrs_world* world, const float* cmds, const uint8_t* cmd_mask,
+                          float* ranges_out, int32_t* hit_idx_out);
+int umrs_world_wait_outputs(umrs_world* world, int32_t ticks_back);
+int umrs_world_wait(umrs_world* world);
 /* Device version: cmds/mask already on the device, results stay there.  Async on
  * stream (cudaStream_t as void*; NULL = the handle's own stream). */
 int umrs_world_step_device(umrs_world* world, const float* cmds_dev,

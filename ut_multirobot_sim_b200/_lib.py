@@ -118,6 +118,9 @@ SIGNATURES = {
     "umrs_world_set_static_objects": (C.c_int, [_P, _F]),
     "umrs_world_get_object_lines": (C.c_int, [_P, _F]),
     "umrs_world_step": (C.c_int, [_P, _P, _P, _P, _P]),
+    "umrs_world_step_async": (C.c_int, [_P, _P, _P, _P, _P]),
+    "umrs_world_wait_outputs": (C.c_int, [_P, C.c_int32]),
+    "umrs_world_wait": (C.c_int, [_P]),
     "umrs_world_step_device": (C.c_int, [_P, _P, _P, _P]),
     "umrs_world_device_buffers": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
     "umrs_world_get_fan_params": (C.c_int, [_P, _F]),

@@ -253,6 +253,17 @@ class World:
         """Host-buffer step on raw addresses (e.g. pinned torch tensors' data_ptr())."""
         check(self._lib.umrs_world_step(self._h, cmds_ptr, mask_ptr, ranges_ptr, idx_ptr), "umrs_world_step")
 
+    def step_async_raw(self, cmds_ptr, mask_ptr, ranges_ptr, idx_ptr):
+        """Pipelined host-buffer tick on raw addresses (pinned buffers); see wait_outputs / wait."""
+        check(self._lib.umrs_world_step_async(self._h, cmds_ptr, mask_ptr, ranges_ptr, idx_ptr),
+              "umrs_world_step_async")
+
+    def wait_outputs(self, ticks_back=0):
+        check(self._lib.umrs_world_wait_outputs(self._h, int(ticks_back)), "umrs_world_wait_outputs")
+
+    def wait(self):
+        check(self._lib.umrs_world_wait(self._h), "umrs_world_wait")
+
     def step_device(self, cmds_dev_ptr, mask_dev_ptr=None, stream=None):
         check(self._lib.umrs_world_step_device(self._h, cmds_dev_ptr, mask_dev_ptr, stream),
               "umrs_world_step_device")

@@ -48,6 +48,12 @@ struct umrs_world {
   cudaStream_t stream = nullptr;
   cudaStream_t copy_stream = nullptr;   // device->host copies of finished slices
   cudaEvent_t slice_done[kMaxSlices] = {};
+  // pipelined host-buffer ticks (umrs_world_step_async): copy of slice s of the previous tick,
+  // and whole-tick completion, both recorded on the copy stream
+  cudaEvent_t copy_done[kMaxSlices] = {};
+  cudaEvent_t tick_done[4] = {};
+  uint64_t async_ticks = 0;
+  bool async_pending = false;
   uint64_t step = 0;
   int cur = 0;  // index of the "in" state buffer
   // device
@@ -96,6 +102,10 @@ int umrs_world_destroy(umrs_world* w) {
   if (w->stream) cudaStreamDestroy(w->stream);
   if (w->copy_stream) cudaStreamDestroy(w->copy_stream);
   for (cudaEvent_t e : w->slice_done)
+    if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : w->copy_done)
+    if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : w->tick_done)
     if (e) cudaEventDestroy(e);
   delete w;
   return UMRS_OK;
@@ -194,6 +204,10 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (ok()) e = cudaStreamCreateWithFlags(&w->copy_stream, cudaStreamNonBlocking);
   for (int k = 0; k < kMaxSlices; ++k)
     if (ok()) e = cudaEventCreateWithFlags(&w->slice_done[k], cudaEventDisableTiming);
+  for (int k = 0; k < kMaxSlices; ++k)
+    if (ok()) e = cudaEventCreateWithFlags(&w->copy_done[k], cudaEventDisableTiming);
+  for (int k = 0; k < 4; ++k)
+    if (ok()) e = cudaEventCreateWithFlags(&w->tick_done[k], cudaEventDisableTiming);
   if (ok()) e = dalloc(&w->d_robots, (size_t)w->R);
   if (ok()) e = dalloc(&w->d_humans, (size_t)w->H);
   if (ok()) e = dalloc(&w->d_tmpl, (size_t)w->L_obj);
@@ -447,8 +461,14 @@ int umrs_world_step_device(umrs_world* w, const float* cmds_dev, const uint8_t* 
   return world_launch(w, cmds_dev, mask_dev, stream ? (cudaStream_t)stream : w->stream, 0, w->W, true);
 }
 
-int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
-                    float* ranges_out, int32_t* hit_idx_out) {
+}  // extern "C"
+
+// One tick with host buffers, enqueued on the world's two streams (no synchronisation here).
+// pipelined: this tick may follow one whose device->host copies are still running -- a slice's
+// kernel then waits for the previous tick's copy of the same slice (it overwrites that part
+// of d_ranges), and the tick's completion is recorded for umrs_world_wait_outputs.
+static int step_enqueue(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
+                        float* ranges_out, int32_t* hit_idx_out, bool pipelined) {
   if (w == NULL) return UMRS_ERR_INVALID;
   if (hit_idx_out != NULL && w->d_idx == NULL) return UMRS_ERR_INVALID;   // also: reference-render worlds
   const size_t WR = (size_t)w->W * w->R;
@@ -470,6 +490,7 @@ int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
   for (int s = 0; s < n_slices; ++s) {
     const int32_t first = (int32_t)((int64_t)w->W * s / n_slices);
     const int32_t end = (int32_t)((int64_t)w->W * (s + 1) / n_slices);
+    if (w->async_pending) UMRS_CUDA(cudaStreamWaitEvent(w->stream, w->copy_done[s], 0));
     int st = world_launch(w, dc, dm, w->stream, first, end - first, s == n_slices - 1);
     if (st != UMRS_OK) return st;
     if (ranges_out == NULL && hit_idx_out == NULL) continue;
@@ -482,9 +503,48 @@ int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
     if (hit_idx_out)
       UMRS_CUDA(cudaMemcpyAsync(hit_idx_out + off, w->d_idx + off, sizeof(int32_t) * cnt,
                                 cudaMemcpyDeviceToHost, w->copy_stream));
+    if (pipelined) UMRS_CUDA(cudaEventRecord(w->copy_done[s], w->copy_stream));
   }
+  if (pipelined) {
+    // the tick is complete when its kernels AND its copies are
+    UMRS_CUDA(cudaEventRecord(w->slice_done[kMaxSlices - 1], w->stream));
+    UMRS_CUDA(cudaStreamWaitEvent(w->copy_stream, w->slice_done[kMaxSlices - 1], 0));
+    UMRS_CUDA(cudaEventRecord(w->tick_done[w->async_ticks & 3], w->copy_stream));
+    w->async_ticks += 1;
+    w->async_pending = ranges_out != NULL || hit_idx_out != NULL;
+  }
+  return UMRS_OK;
+}
+
+extern "C" {
+
+int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
+                    float* ranges_out, int32_t* hit_idx_out) {
+  const int st = step_enqueue(w, cmds, cmd_mask, ranges_out, hit_idx_out, false);
+  if (st != UMRS_OK) return st;
   UMRS_CUDA(cudaStreamSynchronize(w->stream));
   UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
+  w->async_pending = false;
+  return UMRS_OK;
+}
+
+int umrs_world_step_async(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
+                          float* ranges_out, int32_t* hit_idx_out) {
+  return step_enqueue(w, cmds, cmd_mask, ranges_out, hit_idx_out, true);
+}
+
+int umrs_world_wait_outputs(umrs_world* w, int32_t ticks_back) {
+  if (w == NULL || ticks_back < 0 || ticks_back > 2) return UMRS_ERR_INVALID;
+  if (w->async_ticks <= (uint64_t)ticks_back) return UMRS_OK;   // nothing that old was issued
+  UMRS_CUDA(cudaEventSynchronize(w->tick_done[(w->async_ticks - 1 - (uint64_t)ticks_back) & 3]));
+  return UMRS_OK;
+}
+
+int umrs_world_wait(umrs_world* w) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  UMRS_CUDA(cudaStreamSynchronize(w->stream));
+  UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
+  w->async_pending = false;
   return UMRS_OK;
 }
 
