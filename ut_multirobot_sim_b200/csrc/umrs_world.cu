@@ -481,8 +481,15 @@ static int step_enqueue(umrs_world* w, const float* cmds, const uint8_t* cmd_mas
   // instead of their sum.  Worlds are independent, so slicing changes nothing else.
   const float* dc = cmds ? w->d_cmds : nullptr;
   const uint8_t* dm = (cmds && cmd_mask) ? w->d_mask : nullptr;
+  // synchronous tick: 8 slices (first-slice latency matters); pipelined ticks: 4 (in steady state
+  // the copy engine never idles and fewer, larger copies run faster) -- measured on B200
+  if (!pipelined && w->async_pending) {
+    // a blocking tick after pipelined ones slices differently: let their copies finish first
+    UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
+    w->async_pending = false;
+  }
   int n_slices = 1;
-  if (ranges_out != NULL && w->W >= 1024) n_slices = 8;
+  if (ranges_out != NULL && w->W >= 1024) n_slices = pipelined ? 4 : 8;
   if (const char* e = getenv("UMRS_STEP_SLICES")) n_slices = atoi(e) > 0 ? atoi(e) : 1;
   if (n_slices > w->W) n_slices = w->W;
   if (n_slices > kMaxSlices) n_slices = kMaxSlices;
