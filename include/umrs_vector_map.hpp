@@ -106,5 +106,23 @@ class VectorMapT {
   std::vector<float> flat_obj_;
 };
 
+// Fills a sensor_msgs::LaserScan-shaped message the way Simulator::init sets its template
+// (simulator.cpp:150-159) and publishLaser its ranges (simulator.cpp:419-424), from one robot's
+// header (umrs_world_scan_header) and one world's block of the ranges buffer.  LaserScanMsg needs
+// the members angle_min, angle_max, angle_increment, time_increment, scan_time, range_min,
+// range_max, ranges (vector<float>) and intensities (any container with clear()).
+template <class LaserScanMsg>
+void FillLaserScan(const umrs_laser_scan_header& h, const float* world_ranges, LaserScanMsg* msg) {
+  msg->angle_min = h.angle_min;
+  msg->angle_max = h.angle_max;
+  msg->angle_increment = h.angle_increment;
+  msg->time_increment = h.time_increment;
+  msg->scan_time = h.scan_time;
+  msg->range_min = h.range_min;
+  msg->range_max = h.range_max;
+  msg->ranges.assign(world_ranges + h.ranges_offset, world_ranges + h.ranges_offset + h.num_rays);
+  msg->intensities.clear();
+}
+
 }  // namespace umrs
 #endif  // UMRS_VECTOR_MAP_HPP_

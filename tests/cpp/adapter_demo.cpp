@@ -20,7 +20,26 @@ struct Line {
   Line(const Vec2& a, const Vec2& b) : p0(a), p1(b) {}
 };
 
+// stand-in for sensor_msgs::LaserScan (the fields simulator.cpp:150-159 sets)
+struct LaserScanPod {
+  float angle_min, angle_max, angle_increment, time_increment, scan_time, range_min, range_max;
+  std::vector<float> ranges, intensities;
+};
+
+static int CheckFillLaserScan() {
+  umrs_laser_scan_header h = {};
+  h.angle_min = -1.f; h.angle_max = 1.f; h.angle_increment = 0.5f; h.scan_time = 0.05f;
+  h.range_min = 0.4f; h.range_max = 30.f; h.num_rays = 4; h.ranges_offset = 2;
+  const float block[8] = {9, 9, 1, 2, 3, 4, 9, 9};
+  LaserScanPod m;
+  m.intensities.push_back(1.f);
+  umrs::FillLaserScan(h, block, &m);
+  return (m.ranges.size() == 4 && m.ranges[0] == 1.f && m.ranges[3] == 4.f && m.intensities.empty() &&
+          m.angle_increment == 0.5f && m.scan_time == 0.05f && m.range_max == 30.f) ? 0 : 1;
+}
+
 int main(int argc, char** argv) {
+  if (CheckFillLaserScan() != 0) return 4;
   if (argc < 8) return 2;
   try {
     umrs::VectorMapT<Vec2, Line> map_;
