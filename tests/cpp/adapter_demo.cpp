@@ -6,6 +6,9 @@
 #include <cstdlib>
 #include <vector>
 
+#include <cstring>
+
+#include "umrs_robot_model.hpp"
 #include "umrs_vector_map.hpp"
 
 struct Vec2 {
@@ -19,6 +22,39 @@ struct Line {
   Vec2 p0, p1;
   Line(const Vec2& a, const Vec2& b) : p0(a), p1(b) {}
 };
+
+// stand-in for pose_2d::Pose2Df (poses_2d.h:32-104)
+struct Pose {
+  Vec2 translation;
+  float angle;
+  Pose(float a, const Vec2& t) : translation(t), angle(a) {}
+};
+
+// adapter_demo model <map.txt> <ut_automata|ut_jackal|cobot> <x> <y> <theta> <steps> <c0> <c1> <c2>
+// drives include/umrs_robot_model.hpp the way Simulator::update drives a motion model
+// (simulator.cpp:479-486); prints "pose x y theta vx vy w" per step, then the last scan.
+static int RunModel(int argc, char** argv) {
+  if (argc < 11) return 2;
+  umrs::VectorMapT<Vec2, Line> map_;
+  map_.Load(argv[2]);
+  umrs_robot_params rp;
+  if (!std::strcmp(argv[3], "ut_jackal")) umrs_default_ut_jackal(&rp);
+  else if (!std::strcmp(argv[3], "cobot")) umrs_default_cobot(&rp);
+  else umrs_default_ut_automata(&rp);
+  umrs::RobotModelT<Pose, Vec2, Line> model(map_.handle(), rp, 0.025f);
+  model.SetPose(Pose(atof(argv[6]), Vec2(atof(argv[4]), atof(argv[5]))));
+  const int steps = atoi(argv[7]);
+  for (int s = 0; s < steps; ++s) {
+    if (s % 3 != 2) model.DriveCallback(atof(argv[8]), atof(argv[9]), atof(argv[10]));   // a gap every third tick
+    model.Step(0.025f);
+    const Pose p = model.GetPose(), v = model.GetVel();
+    std::printf("pose %.9g %.9g %.9g %.9g %.9g %.9g\n", p.translation.x(), p.translation.y(), p.angle,
+                v.translation.x(), v.translation.y(), v.angle);
+  }
+  std::printf("body %zu rays %d\n", model.GetLines().size(), model.header().num_rays);
+  for (float r : model.ranges()) std::printf("%.9g\n", r);
+  return 0;
+}
 
 // stand-in for sensor_msgs::LaserScan (the fields simulator.cpp:150-159 sets)
 struct LaserScanPod {
@@ -40,6 +76,14 @@ static int CheckFillLaserScan() {
 
 int main(int argc, char** argv) {
   if (CheckFillLaserScan() != 0) return 4;
+  if (argc > 1 && !std::strcmp(argv[1], "model")) {
+    try {
+      return RunModel(argc, argv);
+    } catch (const std::exception& e) {
+      std::fprintf(stderr, "%s\n", e.what());
+      return 3;
+    }
+  }
   if (argc < 8) return 2;
   try {
     umrs::VectorMapT<Vec2, Line> map_;
