@@ -352,3 +352,35 @@ def test_occlusion_cull_random_clutter_many_fans(oracle):
     rb, ib = vmap.ScanBatch(fans, 40.0, 1081, return_index=True)
     for k, f in enumerate(fans):
         check_against_tierb(oracle, segs, None, f, 40.0, 1081, rb[k], ib[k])
+
+
+def test_random_raw_maps_with_degenerate_geometry(oracle):
+    """The default scan on 150 small RAW lattice maps (crossings, shared end points, collinear
+    overlaps, duplicates, zero-length lines) from poses that are often exactly on a line or an end
+    point: the tier-B contract holds on every ray (non-finite oracle ranges must be non-finite
+    here too)."""
+    rng = np.random.default_rng(78)
+    for trial in range(150):
+        n = int(rng.integers(1, 50))
+        step = float(rng.choice([0.5, 1.0, 2.0]))
+        raw = (rng.integers(-10, 11, (n, 4)) * step).astype(np.float32)
+        if trial % 4 == 0:
+            raw[rng.integers(0, n)] = np.repeat(raw[rng.integers(0, n), :2], 2)[[0, 2, 1, 3]]
+        vmap = umrs.VectorMap(lines=raw)
+        m = 8
+        locs = rng.integers(-10, 11, (m, 2)) * step * rng.choice([1.0, 0.5], (m, 1))
+        if trial % 2 == 0:
+            locs = locs + rng.normal(0, 0.3, (m, 2))
+        th = rng.uniform(-np.pi, np.pi, m)
+        d135 = np.float32(np.pi * 0.75)
+        fans = np.stack([locs[:, 0], locs[:, 1], th - d135, th + d135], 1).astype(np.float32)
+        r, i = vmap.ScanBatch(fans, 25.0, 181, return_index=True)
+        for k, f in enumerate(fans):
+            r_o, i_o = oracle.scan_tierb(raw, None, f[:2], 25.0, f[2], f[3], 181)
+            fin = np.isfinite(r_o)
+            assert np.array_equal(np.isfinite(r[k]), fin), (trial, k)
+            if fin.all():
+                check_against_tierb(oracle, raw, None, f, 25.0, 181, r[k], i[k])
+            else:
+                rel = np.abs(r[k][fin] - r_o[fin]) / np.maximum(np.abs(r_o[fin]), 1e-9)
+                assert rel.max() <= REL_TOL, (trial, k)

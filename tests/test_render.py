@@ -216,3 +216,38 @@ def test_gpu_reference_render_warp_per_fan_and_cta_per_fan_forms_agree(ref):
     assert np.array_equal(big.view(np.uint32), small.view(np.uint32))
     want = rm.scan_batch(fans[::50], 0.4, 100.0, 1081, threads=4)
     assert np.array_equal(big[::50].view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_gpu_reference_render_random_raw_maps_with_degenerate_geometry(ref):
+    """Stress of the trimming predicates: 150 small RAW maps (no Cleanup) on a coarse lattice --
+    crossing segments, shared end points, collinear overlaps, duplicates, zero-length lines, the
+    laser exactly on a line or on an end point -- every range equals the reference's, bit for bit
+    (NaN and infinite ranges included, compared as bit patterns)."""
+    import ut_multirobot_sim_b200 as umrs
+    rng = np.random.default_rng(77)
+    rays = 0
+    for trial in range(150):
+        n = int(rng.integers(1, 50))
+        step = float(rng.choice([0.5, 1.0, 2.0]))
+        raw = (rng.integers(-10, 11, (n, 4)) * step).astype(np.float32)
+        if trial % 4 == 0:
+            raw[rng.integers(0, n)] = np.repeat(raw[rng.integers(0, n), :2], 2)[[0, 2, 1, 3]]   # zero-length line
+        vmap = umrs.VectorMap(lines=raw)          # taken as is: the render has to cope, like the reference
+        rm = ref.map_from_segments(raw, False)
+        m = 12
+        locs = rng.integers(-10, 11, (m, 2)) * step * rng.choice([1.0, 0.5], (m, 1))   # often ON the lattice
+        if trial % 2 == 0:
+            locs = locs + rng.normal(0, 0.3, (m, 2))
+        th = rng.uniform(-np.pi, np.pi, m)
+        fans = np.stack([locs[:, 0], locs[:, 1], th - D135, th + D135], 1).astype(np.float32)
+        nr = 181
+        got = vmap.ScanBatchReferenceRender(fans, 25.0, nr)
+        with np.errstate(all="ignore"):
+            want = rm.scan_batch(fans, 0.4, 25.0, nr, threads=1)
+        same = got.view(np.uint32) == want.view(np.uint32)
+        both_nan = np.isnan(got) & np.isnan(want)      # NaN payload/sign may differ between x86 and the GPU
+        assert (same | both_nan).all(), (trial, np.argwhere(~(same | both_nan))[:3], got[~(same | both_nan)][:3],
+                                         want[~(same | both_nan)][:3])
+        rays += got.size
+    assert rays == 150 * 12 * 181
