@@ -184,6 +184,71 @@ class Ref:
         lib.umrs_ref_unit_normal.argtypes = [_F, _F]
         lib.umrs_ref_apply_pose.argtypes = [_F, _F]
         lib.umrs_ref_short_term_object.argtypes = [_F, _F, _F]
+        # the reference's kinematic models (oracle/ref_models_bridge.cpp)
+        self.has_models = hasattr(lib, "umrs_ref_model_create")
+        if self.has_models:
+            lib.umrs_ref_config_set_float.argtypes = [C.c_char_p, C.c_float]
+            lib.umrs_ref_config_set_int.argtypes = [C.c_char_p, C.c_int]
+            lib.umrs_ref_config_set_bool.argtypes = [C.c_char_p, C.c_int]
+            lib.umrs_ref_config_set_string.argtypes = [C.c_char_p, C.c_char_p]
+            lib.umrs_ref_model_create.restype = C.c_void_p
+            lib.umrs_ref_model_create.argtypes = [C.c_int]
+            lib.umrs_ref_model_free.argtypes = [C.c_void_p]
+            for n in ("set_pose", "get_pose", "set_vel", "get_vel", "command"):
+                getattr(lib, "umrs_ref_model_" + n).argtypes = [C.c_void_p, _F]
+                getattr(lib, "umrs_ref_model_" + n).restype = None
+            lib.umrs_ref_model_step.argtypes = [C.c_void_p, C.c_double]
+            lib.umrs_ref_model_step.restype = None
+            lib.umrs_ref_normal_stream.argtypes = [C.c_int, _F]
+            lib.umrs_ref_human_create.restype = C.c_void_p
+            lib.umrs_ref_human_free.argtypes = [C.c_void_p]
+            lib.umrs_ref_human_step.argtypes = [C.c_void_p, C.c_double]
+            lib.umrs_ref_human_set_vel.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_double]
+            lib.umrs_ref_human_set_pose.argtypes = [C.c_void_p, _F]
+            lib.umrs_ref_human_get_pose.argtypes = [C.c_void_p, _F]
+            lib.umrs_ref_human_lines.argtypes = [C.c_void_p, _F, C.c_int]
+            lib.umrs_ref_human_template.argtypes = [C.c_void_p, _F, C.c_int]
+
+    def configure_robot(self, rp):
+        """Fill the ConfigReader slots the three models read with a umrs_robot_params."""
+        L = self.lib
+        for key, field in (("ak_min_turn_radius", "ak_min_turn_radius"), ("ak_max_accel", "ak_max_accel"),
+                           ("ak_max_speed", "ak_max_speed"), ("ak_angular_error_bias", "ak_angular_error_bias"),
+                           ("ak_angular_error_rate", "ak_angular_error_rate"),
+                           ("linear_pos_accel_limit", "linear_pos_accel_limit"),
+                           ("linear_neg_accel_limit", "linear_neg_accel_limit"),
+                           ("angular_pos_accel_limit", "angular_pos_accel_limit"),
+                           ("angular_neg_accel_limit", "angular_neg_accel_limit"),
+                           ("max_angular", "max_angular"), ("max_linear_vel", "max_linear_vel"),
+                           ("co_max_accel", "co_max_accel"), ("co_max_angle_accel", "co_max_angle_accel"),
+                           ("co_max_speed", "co_max_speed"), ("co_max_angle_vel", "co_max_angle_vel")):
+            L.umrs_ref_config_set_float(key.encode(), float(getattr(rp, field)))
+        for key in ("linear_odom_scale", "angular_odom_scale", "co_base_radius"):
+            L.umrs_ref_config_set_float(key.encode(), 1.0)
+        for i in range(4):
+            L.umrs_ref_config_set_float(b"co_w%d" % i, 0.7853981633974483 * (2 * i + 1))
+        L.umrs_ref_config_set_bool(b"invert_linear_vel_cmds", int(rp.invert_linear_vel_cmds))
+        L.umrs_ref_config_set_bool(b"invert_angular_vel_cmds", int(rp.invert_angular_vel_cmds))
+        for key in ("ak_drive_callback_topic", "drive_callback_topic", "diff_drive_odom_topic",
+                    "co_drive_callback_topic", "co_cobot_odom_topic"):
+            L.umrs_ref_config_set_string(key.encode(), b"/" + key.encode())
+
+    def robot_model(self, rp):
+        self.configure_robot(rp)
+        return RefModel(self, self.lib.umrs_ref_model_create(int(rp.model_type)))
+
+    def human(self, hp):
+        L = self.lib
+        for f in ("radius", "num_segments", "start_x", "start_y", "start_theta", "goal_x", "goal_y",
+                  "goal_theta", "max_speed", "avg_speed", "max_omega", "avg_omega", "reach_goal_threshold"):
+            L.umrs_ref_config_set_float(("hu_" + f).encode(), float(getattr(hp, f)))
+        L.umrs_ref_config_set_int(b"hu_mode", int(hp.mode))
+        return RefHuman(self, L.umrs_ref_human_create())
+
+    def normal_stream(self, n):
+        out = np.empty(n, np.float32)
+        self.lib.umrs_ref_normal_stream(n, _fp(out))
+        return out
 
     def map_from_segments(self, segs, cleanup):
         s = np.ascontiguousarray(segs, np.float32).reshape(-1, 4)
@@ -193,6 +258,82 @@ class Ref:
         h = self.lib.umrs_ref_map_load(str(path).encode())
         assert h, "reference could not open %s" % path
         return RefMap(self, h)
+
+
+class RefModel:
+    """One of the reference's own robot models (MakeMotionModel, simulator.cpp:128-142)."""
+
+    def __init__(self, ref, handle):
+        self.ref, self.h = ref, C.c_void_p(handle)
+
+    def _get(self, fn):
+        out = np.empty(3, np.float32)
+        fn(self.h, _fp(out))
+        return out
+
+    def SetPose(self, xyt):
+        self.ref.lib.umrs_ref_model_set_pose(self.h, _fp(np.ascontiguousarray(xyt, np.float32)))
+
+    def SetVel(self, xyt):
+        self.ref.lib.umrs_ref_model_set_vel(self.h, _fp(np.ascontiguousarray(xyt, np.float32)))
+
+    def GetPose(self):
+        return self._get(self.ref.lib.umrs_ref_model_get_pose)
+
+    def GetVel(self):
+        return self._get(self.ref.lib.umrs_ref_model_get_vel)
+
+    def DriveCallback(self, cmd):
+        c = np.zeros(3, np.float32)
+        c[:len(cmd)] = cmd
+        self.ref.lib.umrs_ref_model_command(self.h, _fp(c))
+
+    def Step(self, dt):
+        self.ref.lib.umrs_ref_model_step(self.h, float(dt))
+
+    def __del__(self):
+        try:
+            self.ref.lib.umrs_ref_model_free(self.h)
+        except Exception:
+            pass
+
+
+class RefHuman:
+    """The reference's HumanObject (human_object.cpp)."""
+
+    def __init__(self, ref, handle):
+        self.ref, self.h = ref, C.c_void_p(handle)
+
+    def Step(self, dt):
+        self.ref.lib.umrs_ref_human_step(self.h, float(dt))
+
+    def SetVel(self, vx, vy, rot):
+        self.ref.lib.umrs_ref_human_set_vel(self.h, float(vx), float(vy), float(rot))
+
+    def SetPose(self, xyt):
+        self.ref.lib.umrs_ref_human_set_pose(self.h, _fp(np.ascontiguousarray(xyt, np.float32)))
+
+    def GetPose(self):
+        out = np.empty(3, np.float32)
+        self.ref.lib.umrs_ref_human_get_pose(self.h, _fp(out))
+        return out
+
+    def _lines(self, fn):
+        out = np.empty((64, 4), np.float32)
+        n = fn(self.h, _fp(out), 64)
+        return out[:n].copy()
+
+    def GetLines(self):
+        return self._lines(self.ref.lib.umrs_ref_human_lines)
+
+    def GetTemplateLines(self):
+        return self._lines(self.ref.lib.umrs_ref_human_template)
+
+    def __del__(self):
+        try:
+            self.ref.lib.umrs_ref_human_free(self.h)
+        except Exception:
+            pass
 
 
 class RefMap:
@@ -256,10 +397,11 @@ def load_ref():
     global _ref
     if _ref is None:
         p = os.path.join(ORACLE_DIR, "_ref", "libumrs_ref.so")
+        have_ref = os.path.isdir("/root/reference/src/simulator")
+        srcs = [os.path.join(ORACLE_DIR, f) for f in ("ref_bridge.cpp", "ref_models_bridge.cpp")]
+        if have_ref and (not os.path.exists(p) or any(os.path.getmtime(f) > os.path.getmtime(p) for f in srcs)):
+            build()
         if not os.path.exists(p):
-            if os.path.isdir("/root/reference/src/simulator"):
-                build()
-            else:
-                return None
+            return None
         _ref = Ref(C.CDLL(p))
     return _ref
