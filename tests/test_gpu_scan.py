@@ -308,12 +308,7 @@ def test_back_wedge_cull_keeps_every_covering_segment(oracle):
             check_against_tierb(oracle, segs, None, fan, 50.0, n, r, i)
 
 
-def test_occlusion_cull_against_grazing_and_nested_walls(oracle):
-    """Per-chunk occlusion cull: candidates farther than a wall that certainly covers
-    a whole 32-ray chunk are dropped from that chunk.  Nested boxes (everything
-    behind the inner box is culled), walls seen at grazing angles (ill-conditioned:
-    must neither occlude nor be culled), walls through the laser origin, segments
-    ending inside a chunk, and a far wall visible only through a one-ray gap."""
+def _nested_and_grazing_segments():
     segs = []
     for s in (1.0, 1.0005, 1.001, 2.0, 5.0, 20.0):       # nested boxes, two almost coincident
         segs += [[-s, -s, s, -s], [s, -s, s, s], [s, s, -s, s], [-s, s, -s, -s]]
@@ -329,10 +324,62 @@ def test_occlusion_cull_against_grazing_and_nested_walls(oracle):
     # grazing walls and walls through the origin
     graz = np.array([[0.3, 1e-4, 30.0, 2e-4], [-25.0, 0.0, 25.0, 0.0], [0.2, 0.2, 15.0, 15.0001],
                      [1e-3, -3.0, 1.2e-3, 3.0], [0.5, 0.0, 0.9, 0.0]], np.float32)
-    segs = np.concatenate([segs, graz])
+    return np.concatenate([segs, graz])
+
+
+def test_occlusion_cull_against_grazing_and_nested_walls(oracle):
+    """Per-chunk occlusion cull: candidates farther than a wall that certainly covers
+    a whole 32-ray chunk are dropped from that chunk.  Nested boxes (everything
+    behind the inner box is culled), walls seen at grazing angles (ill-conditioned:
+    must neither occlude nor be culled), walls through the laser origin, segments
+    ending inside a chunk, and a far wall visible only through a one-ray gap."""
+    segs = _nested_and_grazing_segments()
     vmap = umrs.VectorMap(lines=segs)
     for loc in ((0.0, 0.0), (0.013, -0.4), (0.9, 0.9), (-0.999, 0.5), (1.5, 0.0), (0.0, 1.00025)):
         for amin, amax, n in ((-2.356, 2.356, 1081), (-np.pi, np.pi, 3601), (0.5, 7.0, 2048), (-0.05, 0.05, 64)):
+            fan = np.array([loc[0], loc[1], amin, amax], np.float32)
+            r, i = vmap.GetPredictedScan(fan[:2], 0.4, 30.0, fan[2], fan[3], n, return_index=True)
+            check_against_tierb(oracle, segs, None, fan, 30.0, n, r, i)
+
+
+def test_coarse_precull_keeps_every_winner(oracle):
+    """The coarse occlusion pre-cull (S1b) runs once a fan gathers more candidates than the CTA
+    has threads.  The nested / grazing / through-the-origin walls above, buried in 700 far
+    segments so that it does run: short far segments whose end-point angles differ by less than
+    the coarse atan error (the arc-order guard), radial segments (nearest point = an end point),
+    tangential ones (nearest point interior), long far walls spanning many chunks, and segments
+    placed at 1.0005x / 1.002x the distance of a wall that covers their chunk (either side of
+    the cull margin).  Tier-B contract on every ray, hit index included."""
+    rng = np.random.default_rng(2024)
+    base = _nested_and_grazing_segments()
+    far = []
+    for k in range(300):                                   # short, any orientation, ring 21..29 m
+        a, r = rng.uniform(-np.pi, np.pi), rng.uniform(21.0, 29.0)
+        c = np.array([r * np.cos(a), r * np.sin(a)])
+        d = rng.normal(0, 1.0, 2)
+        d *= rng.choice([0.03, 0.06, 0.5, 2.0]) / np.linalg.norm(d)
+        far.append(np.concatenate([c - d, c + d]))
+    for k in range(150):                                   # radial: seen end-on
+        a, r0, ln = rng.uniform(-np.pi, np.pi), rng.uniform(5.5, 25.0), rng.uniform(0.1, 4.0)
+        off = rng.choice([0.0, 1e-3, 0.05, 0.3])           # line passes this close to the origin
+        u, v = np.array([np.cos(a), np.sin(a)]), np.array([-np.sin(a), np.cos(a)])
+        far.append(np.concatenate([r0 * u + off * v, (r0 + ln) * u + off * v]))
+    for k in range(150):                                   # tangential, some long
+        a, r = rng.uniform(-np.pi, np.pi), rng.uniform(5.5, 28.0)
+        h = rng.choice([0.2, 2.0, 12.0])
+        u, v = np.array([np.cos(a), np.sin(a)]), np.array([-np.sin(a), np.cos(a)])
+        far.append(np.concatenate([r * u - h * v, r * u + h * v]))
+    for f in (1.0002, 1.0005, 1.001, 1.002, 1.01):        # just behind the s = 5 box's corners
+        for sx, sy in ((1, 1), (-1, 1), (-1, -1), (1, -1)):
+            cx, cy = 5.0 * f * sx, 5.0 * f * sy
+            far.append([cx - 0.2 * sy, cy + 0.2 * sx, cx + 0.2 * sy, cy - 0.2 * sx])
+        far.append([5.0 * f, -1.0, 5.0 * f, 1.0])         # and parallel to its +x wall
+    segs = np.concatenate([base, np.asarray(far, np.float32)]).astype(np.float32)
+    vmap = umrs.VectorMap(lines=segs)
+    for loc in ((0.0, 0.0), (0.013, -0.4), (0.9, 0.9), (-0.999, 0.5), (1.5, 0.0), (0.0, 1.00025),
+                (3.0, 3.0), (-7.0, 2.0), (12.0, -12.0)):
+        for amin, amax, n in ((-2.356, 2.356, 1081), (-np.pi, np.pi, 3601), (0.5, 7.0, 2048),
+                              (-0.05, 0.05, 64), (2.0, 4.5, 37)):
             fan = np.array([loc[0], loc[1], amin, amax], np.float32)
             r, i = vmap.GetPredictedScan(fan[:2], 0.4, 30.0, fan[2], fan[3], n, return_index=True)
             check_against_tierb(oracle, segs, None, fan, 30.0, n, r, i)

@@ -19,6 +19,9 @@
 //      grid rows overlapping [loc +- range_max] for K2; then the object lines),
 //      apply the reference's AABB cull and compact the survivors' translated
 //      end points + hit index into shared memory (warp ballot + one atomic)
+//   S1b pre-cull (fans with more candidates than threads): coarse angles and
+//      distances drop every candidate that lies wholly behind a wall covering
+//      its chunks, before any exact work is spent on it
 //   S2 records: one thread per survivor: lazily exact end-point angles, swap,
 //      unit normal -> {a0,a1,nx,ny | c}; conservative ray-index span; the span
 //      is turned into per-32-ray-chunk BUCKETS (count, scan, fill) so that the
@@ -66,6 +69,7 @@ struct SmemView {
                      //   S2: {a0, a1, nx, ny}             | {c = n . p0', hit index, -, -}
   uint16_t* pool;    // [3*cap] bucket entries (slots): chunk c owns [c*K, (c+1)*K)
   uint16_t* wide;    // [cap/2] slots of candidates that met a full bucket: span-checked per chunk
+  uint16_t* surv;    // [cap] slots that survived the coarse occlusion pre-cull (S1b)
   float* best_r;     // [max_rays] range of the running winner (the reference's exact expression)
   float* best_q;     // [max_rays] the quotient the winner was selected on (multi-pass plans only)
   int32_t* best_i;   // [max_rays] its hit index (-1: none)
@@ -73,12 +77,12 @@ struct SmemView {
   uint32_t* zmax2;   // [n_chunks_max] float bits: squared distance beyond which nothing in the chunk can win
   int32_t* row_v0;   // [max_rows + 1] first virtual index of source row r
   int32_t* row_s0;   // [max_rows] first source index of row r (object row: 0)
-  int32_t* ctl;      // [16] n_cand, wide overflow, n_wide, next_chunk, n_rows, wedge flag, -, -, wedge[4]
+  int32_t* ctl;      // [16] n_cand, wide overflow, n_wide, next_chunk, n_rows, wedge flag, n_surv, -, wedge[4]
   float4* obj;       // [n_obj_lines] world object lines (world step only)
   float* ent;        // [n_ent][8] {x, y, theta, sin, cos (AngleMod theta), sin, cos (theta), -} (world step only)
 };
 enum { kCtlNCand = 0, kCtlWideOverflow = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4,
-       kCtlWedgeOn = 5, kCtlWedge = 8 /* 4 floats: e1x, e1y, e2x, e2y */ };
+       kCtlWedgeOn = 5, kCtlNSurv = 6, kCtlWedge = 8 /* 4 floats: e1x, e1y, e2x, e2y */ };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
@@ -95,7 +99,7 @@ __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int ma
   const size_t n_chunks = (size_t)((max_rays + 31) >> 5);
   const size_t sizes[16] = {
       sizeof(float4) * 2 * (size_t)cap,        // rec
-      0,                                       // (spare)
+      sizeof(uint16_t) * (size_t)cap,          // surv
       0,                                       // (spare)
       0,                                       // (spare)
       sizeof(uint16_t) * pool_entries(cap, (int)n_chunks),  // pool
@@ -125,24 +129,31 @@ size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int
   return smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent, multipass).o[16];
 }
 
-__device__ inline SmemView carve(unsigned char* base, int cap, int max_rows, int max_rays,
-                                 int n_obj_lines, int n_ent, int multipass) {
-  const SmemOffsets L = smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent, multipass);
+// The offsets come with the launch parameters (constant bank): see fill_smem_offsets.
+__device__ __forceinline__ SmemView carve(unsigned char* base, const ScanCommon& c) {
   SmemView v;
-  v.rec = reinterpret_cast<float4*>(base + L.o[0]);
-  v.pool = reinterpret_cast<uint16_t*>(base + L.o[4]);
-  v.wide = reinterpret_cast<uint16_t*>(base + L.o[5]);
-  v.best_r = reinterpret_cast<float*>(base + L.o[6]);
-  v.best_i = reinterpret_cast<int32_t*>(base + L.o[7]);
-  v.cnt = reinterpret_cast<int32_t*>(base + L.o[8]);
-  v.zmax2 = reinterpret_cast<uint32_t*>(base + L.o[9]);
-  v.row_v0 = reinterpret_cast<int32_t*>(base + L.o[10]);
-  v.row_s0 = reinterpret_cast<int32_t*>(base + L.o[11]);
-  v.ctl = reinterpret_cast<int32_t*>(base + L.o[12]);
-  v.obj = reinterpret_cast<float4*>(base + L.o[13]);
-  v.ent = reinterpret_cast<float*>(base + L.o[14]);
-  v.best_q = reinterpret_cast<float*>(base + L.o[15]);
+  v.rec = reinterpret_cast<float4*>(base + c.smem_off[0]);
+  v.surv = reinterpret_cast<uint16_t*>(base + c.smem_off[1]);
+  v.pool = reinterpret_cast<uint16_t*>(base + c.smem_off[4]);
+  v.wide = reinterpret_cast<uint16_t*>(base + c.smem_off[5]);
+  v.best_r = reinterpret_cast<float*>(base + c.smem_off[6]);
+  v.best_i = reinterpret_cast<int32_t*>(base + c.smem_off[7]);
+  v.cnt = reinterpret_cast<int32_t*>(base + c.smem_off[8]);
+  v.zmax2 = reinterpret_cast<uint32_t*>(base + c.smem_off[9]);
+  v.row_v0 = reinterpret_cast<int32_t*>(base + c.smem_off[10]);
+  v.row_s0 = reinterpret_cast<int32_t*>(base + c.smem_off[11]);
+  v.ctl = reinterpret_cast<int32_t*>(base + c.smem_off[12]);
+  v.obj = reinterpret_cast<float4*>(base + c.smem_off[13]);
+  v.ent = reinterpret_cast<float*>(base + c.smem_off[14]);
+  v.best_q = reinterpret_cast<float*>(base + c.smem_off[15]);
   return v;
+}
+
+// Host side of carve(): returns the CTA's dynamic shared-memory size.
+static size_t fill_smem_offsets(ScanCommon& c, int n_obj_lines, int n_ent) {
+  const SmemOffsets L = smem_layout(c.cap, c.max_rows, c.max_rays, n_obj_lines, n_ent, c.multipass);
+  for (int k = 0; k < 16; ++k) c.smem_off[k] = (uint32_t)L.o[k];
+  return L.o[16];
 }
 
 struct Fan {
@@ -350,12 +361,137 @@ __device__ __forceinline__ void lower_zmax(const SmemView& sm, int li, int hi, i
   for (int c = ca; c <= cb; ++c) atomicMin(&sm.zmax2[c], bits);
 }
 
-__device__ void make_records(const SmemView& sm, const Lattice& L, unsigned long long* counters) {
+// 1 / x to 1 ulp, one MUFU.RCP (no denormal-scaling wrapper around it).
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// ---- S1b: coarse occlusion pre-cull ------------------------------------------------------
+// Most gathered candidates are walls behind nearer walls.  Before the expensive S2
+// work (exact end-point angles, normals, buckets) a cheap pass drops those that
+// cannot win on ANY ray, with the same argument as the per-chunk cull of S2 (below)
+// but on coarse quantities only:
+//   * approximate end-point angles (polynomial atan, |error| < 2e-5 rad; every use
+//     carries kPreSlack = 1e-3 rad of margin on top of the S2 index margins);
+//   * mind2 = squared distance origin -> segment (a lower bound of every hit range
+//     on the segment), maxd2 = farthest end point (an upper bound);
+//   * only WELL-CONDITIONED segments take part, as occluder or as occluded:
+//     c^2 > 1.2e-4 maxd2 on the coarse c implies the c^2 > 1e-4 maxd2 of the S2
+//     argument for the exact c (the coarse c^2 is within 1e-4 relative: the cross
+//     product is taken against the short edge vector, so it does not cancel).  For
+//     these the reference's a0 -> a1 order is the geometric CCW order (their arc is
+//     in [1e-4, pi - 0.02]; an arc the coarse angles cannot order comes out near 2 pi
+//     and disqualifies the segment), so the exact coverage interval lies inside the
+//     widened coarse span, and contains the narrowed one.
+// Pass 1 lowers zmax2[c] for every chunk an occluder certainly covers; after a barrier
+// pass 2 keeps X iff it is not well-conditioned or some chunk its widened span touches
+// has mind2(X) <= 1.002 zmax2[c].  A dropped X loses, by > 0.05 %, on every ray it
+// covers, to a candidate that stays (an occluder Y of chunk c has maxd2(Y) >= zmax2[c],
+// so Y itself is kept in c), hence neither the minimum nor a tie can involve it.
+// zmax2 is kept for S2, whose own lowering can only tighten it.  Survivors are
+// compacted into sm.surv; a dropped slot gets a0 = a1 = NaN (for the sweep-all path).
+constexpr float kPreWell = 1.2e-4f;
+constexpr float kPreMargin = 1.002f;
+constexpr float kPreSlack = 1e-3f;
+#ifndef UMRS_PRECULL_MIN   // dev builds: 1 << 30 switches S1b off
+#define UMRS_PRECULL_MIN kScanThreads
+#endif
+constexpr int kPreMinCand = UMRS_PRECULL_MIN;   // fewer candidates than threads: S2 is one trip anyway
+
+// atan2 to 2e-5 rad (Abramowitz & Stegun 4.4.49 on the octant-reduced ratio).
+__device__ __forceinline__ float atan2_coarse(float y, float x) {
+  const float ax = fabsf(x), ay = fabsf(y);
+  const float z = fminf(ax, ay) * rcp_approx(fmaxf(ax, ay));
+  const float z2 = z * z;
+  float r = __fmaf_rn(z2, 0.0208351f, -0.0851330f);
+  r = __fmaf_rn(z2, r, 0.1801410f);
+  r = __fmaf_rn(z2, r, -0.3302995f);
+  r = __fmaf_rn(z2, r, 0.9998660f);
+  r *= z;
+  if (ay > ax) r = 1.57079633f - r;
+  if (x < 0.f) r = 3.14159265f - r;
+  return y < 0.f ? -r : r;
+}
+
+__device__ void precull_mark(const SmemView& sm, const Lattice& L) {
+  const int n_cand = sm.ctl[kCtlNCand];
+  const int last = L.num_rays - 1, n_chunks = (L.num_rays + 31) >> 5;
+  const int m = (int)(kPreSlack * L.inv_da) + 2;
+  for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
+    const float4 p = sm.rec[2 * slot];
+    const float ex = p.z - p.x, ey = p.w - p.y;
+    const float d0 = __fmaf_rn(p.x, p.x, p.y * p.y), d1 = __fmaf_rn(p.z, p.z, p.w * p.w);
+    const float maxd2 = fmaxf(d0, d1);
+    const float len2 = __fmaf_rn(ex, ex, ey * ey);
+    const float cr = __fmaf_rn(p.x, ey, -(p.y * ex));       // cross(p0, p1 - p0) = |c| * len
+    const float c2 = (cr * cr) * rcp_approx(len2);
+    int packed = -1;   // -1: takes no part (always survives)
+    float mind2 = 0.f;
+    if (c2 > kPreWell * maxd2 && c2 <= maxd2) {   // NaN / inf: false
+      float aa = atan2_coarse(p.y, p.x), ab = atan2_coarse(p.w, p.z);
+      if (cr < 0.f) { const float t = aa; aa = ab; ab = t; }
+      float arc = ab - aa;
+      if (arc < 0.f) arc += k2PiF;
+      if (arc < 3.2f) {
+        float u0 = aa - L.amin;
+        u0 -= k2PiF * floorf(u0 * (1.0f / k2PiF));
+        const int lo = (int)floorf(u0 * L.inv_da) - m, hi = (int)ceilf((u0 + arc) * L.inv_da) + m;
+        const float dot0 = -__fmaf_rn(p.x, ex, p.y * ey);
+        mind2 = dot0 <= 0.f ? d0 : (dot0 >= len2 ? d1 : c2);
+        packed = pack_ranges(chunk_ranges(lo, hi, L));
+        const uint32_t bits = __float_as_uint(maxd2);
+        const int li = lo + 2 * m + 2, ui = hi - 2 * m - 2;
+        lower_zmax(sm, li, ui, last, n_chunks, bits);
+        lower_zmax(sm, li - L.p_lo, ui - L.p_hi, last, n_chunks, bits);
+      }
+    }
+    float4* r2 = sm.rec + 2 * slot + 1;
+    r2->z = __int_as_float(packed);
+    r2->w = mind2;
+  }
+}
+
+__device__ void precull_compact(const SmemView& sm) {
+  const int n_cand = sm.ctl[kCtlNCand];
+  const int lane = threadIdx.x & 31;
+  const float nanf_ = __int_as_float(0x7fc00000);
+  for (int sb = (int)(threadIdx.x & ~31u); sb < n_cand; sb += blockDim.x) {
+    const int slot = sb + lane;
+    bool keep = false;
+    if (slot < n_cand) {
+      const float4 r2 = sm.rec[2 * slot + 1];
+      const int packed = __float_as_int(r2.z);
+      if (packed < 0) {
+        keep = true;
+      } else {
+        for (int part = 0; part < 2 && !keep; ++part) {
+          const int ca = part ? 0 : (packed & 1023);
+          const int cb = part ? ((packed >> 20) & 1023) - 1 : ((packed >> 10) & 1023);
+          for (int c = ca; c <= cb; ++c)
+            if (!(r2.w > kPreMargin * __uint_as_float(sm.zmax2[c]))) { keep = true; break; }
+        }
+        if (!keep) sm.rec[2 * slot] = make_float4(nanf_, nanf_, 0.f, 0.f);
+      }
+    }
+    const unsigned mk = __ballot_sync(0xffffffffu, keep);
+    int base = 0;
+    if (lane == 0 && mk) base = atomicAdd(&sm.ctl[kCtlNSurv], __popc(mk));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (keep) sm.surv[base + __popc(mk & ((1u << lane) - 1u))] = (uint16_t)slot;
+  }
+}
+
+__device__ void make_records(const SmemView& sm, const Lattice& L, bool listed,
+                             unsigned long long* counters) {
   const int n_cand = sm.ctl[kCtlNCand];
   const float nanf_ = __int_as_float(0x7fc00000);
   const int last = L.num_rays - 1, n_chunks = (L.num_rays + 31) >> 5;
   int n_valid = 0;
-  for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
+  const int n_list = listed ? sm.ctl[kCtlNSurv] : n_cand;
+  for (int j = threadIdx.x; j < n_list; j += blockDim.x) {
+    const int slot = listed ? (int)sm.surv[j] : j;
     const float4 p = sm.rec[2 * slot];
     const SegCast k = make_cast(p.x, p.y, p.z, p.w, L);
     float4 rec = make_float4(nanf_, nanf_, 0.f, 0.f);
@@ -395,9 +531,10 @@ __device__ void make_records(const SmemView& sm, const Lattice& L, unsigned long
   }
 }
 
-__device__ void fill_buckets(const SmemView& sm, int K, int wide_cap) {
-  const int n_cand = sm.ctl[kCtlNCand];
-  for (int slot = threadIdx.x; slot < n_cand; slot += blockDim.x) {
+__device__ void fill_buckets(const SmemView& sm, int K, int wide_cap, bool listed) {
+  const int n_list = listed ? sm.ctl[kCtlNSurv] : sm.ctl[kCtlNCand];
+  for (int j = threadIdx.x; j < n_list; j += blockDim.x) {
+    const int slot = listed ? (int)sm.surv[j] : j;
     const float4 r1 = sm.rec[2 * slot];
     if (!(r1.x == r1.x)) continue;   // not a candidate
     const float4 r2 = sm.rec[2 * slot + 1];
@@ -428,13 +565,6 @@ __device__ void fill_buckets(const SmemView& sm, int K, int wide_cap) {
       else sm.ctl[kCtlWideOverflow] = 1;   // ray loop falls back to sweeping every slot
     }
   }
-}
-
-// 1 / x to 1 ulp, one MUFU.RCP (no denormal-scaling wrapper around it).
-__device__ __forceinline__ float rcp_approx(float x) {
-  float r;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-  return r;
 }
 
 // Shared-memory loads of the hot loop on 32-bit shared addresses (register +
@@ -653,6 +783,7 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
   const int K = bucket_capacity(c.cap, (c.max_rays + 31) >> 5, n_chunks);
   if (threadIdx.x == 0) build_rows(sm, c.src, fan, n_obj, c.max_rows);
   if (threadIdx.x >= 32 && threadIdx.x < 36) sm.ctl[threadIdx.x - 32] = 0;
+  if (threadIdx.x == 36) sm.ctl[kCtlNSurv] = 0;
   if (threadIdx.x == 64) {
     // wedge of directions behind the fan: CCW from e1 (last ray + margin) to e2
     // (first ray - margin); used only when it is narrower than half a turn
@@ -683,10 +814,19 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     __syncthreads();
     UMRS_STAMP(c.counters, 2);
     if (pass == 0 || sm.ctl[kCtlNCand] > 0) {   // block-uniform: a later pass may be empty
-      make_records(sm, L, c.counters);
+      // S1b pays for itself once S2 would need more than one trip of the CTA
+      // (block-uniform: n_cand is settled behind the barrier above)
+      const bool pre = L.lazy_ok && sm.ctl[kCtlNCand] > kPreMinCand;
+      if (pre) {
+        precull_mark(sm, L);
+        __syncthreads();
+        precull_compact(sm);
+        __syncthreads();
+      }
+      make_records(sm, L, pre, c.counters);
       __syncthreads();
       UMRS_STAMP(c.counters, 3);
-      fill_buckets(sm, K, c.cap / 2);
+      fill_buckets(sm, K, c.cap / 2, pre);
       __syncthreads();
       UMRS_STAMP(c.counters, 4);
       ray_loop(sm, fan, L, K, c.cap / 2, pass, c.multipass != 0, c.counters);
@@ -695,6 +835,7 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     UMRS_STAMP(c.counters, 5);
     if (v0 + c.cap < v_total) {   // another pass: reset the per-pass state
       if (threadIdx.x < 4) sm.ctl[threadIdx.x] = 0;
+      if (threadIdx.x == 4) sm.ctl[kCtlNSurv] = 0;
       for (int k = threadIdx.x; k < n_chunks; k += blockDim.x) sm.cnt[k] = 0;
       __syncthreads();
     }
@@ -715,7 +856,7 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
 __global__ void __launch_bounds__(kScanThreads, UMRS_MIN_CTAS)
 k_scan_batch(const __grid_constant__ ScanBatchParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const SmemView sm = carve(smem_raw, p.c.cap, p.c.max_rows, p.c.max_rays, 0, 0, p.c.multipass);
+  const SmemView sm = carve(smem_raw, p.c);
   for (int f = blockIdx.x; f < p.n_fans; f += gridDim.x) {
     const float4 fp = __ldg(p.fans + f);
     Fan fan;
@@ -905,7 +1046,7 @@ __global__ void __launch_bounds__(kScanThreads, UMRS_MIN_CTAS)
 k_world_step(const __grid_constant__ WorldStepParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int n_ent = p.O + p.H + p.R;
-  const SmemView sm = carve(smem_raw, p.c.cap, p.c.max_rows, p.c.max_rays, p.L_obj, n_ent, p.c.multipass);
+  const SmemView sm = carve(smem_raw, p.c);
   const int w = p.world_first + (int)(blockIdx.x / (unsigned)p.R);
   const int r = (int)(blockIdx.x % (unsigned)p.R);
   const bool owner = (r == 0);
@@ -1064,9 +1205,10 @@ static cudaError_t configure_smem(size_t smem_bytes) {
   return cudaSuccess;
 }
 
-cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream) {
-  if (p.n_fans <= 0) return cudaSuccess;
-  const size_t smem = scan_smem_bytes(p.c.cap, p.c.max_rows, p.c.max_rays, 0, 0, p.c.multipass);
+cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) {
+  if (p_in.n_fans <= 0) return cudaSuccess;
+  ScanBatchParams p = p_in;
+  const size_t smem = fill_smem_offsets(p.c, 0, 0);
   cudaError_t e = configure_smem(smem);
   if (e != cudaSuccess) return e;
   k_scan_batch<<<p.n_fans, kScanThreads, smem, stream>>>(p);
@@ -1074,10 +1216,11 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
-cudaError_t launch_world_step(const WorldStepParams& p, cudaStream_t stream) {
-  const int fans = p.world_count * p.R;
+cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) {
+  const int fans = p_in.world_count * p_in.R;
   if (fans <= 0) return cudaSuccess;
-  size_t smem = scan_smem_bytes(p.c.cap, p.c.max_rows, p.c.max_rays, p.L_obj, p.O + p.H + p.R, p.c.multipass);
+  WorldStepParams p = p_in;
+  size_t smem = fill_smem_offsets(p.c, p.L_obj, p.O + p.H + p.R);
   if (const char* pad = getenv("UMRS_SMEM_PAD")) smem += (size_t)atoi(pad);  // occupancy experiments
   cudaError_t e = configure_smem(smem);
   if (e != cudaSuccess) return e;
