@@ -105,9 +105,13 @@ def config4():
         _lib.check(lib.umrs_scan_batch_device(vmap._h, None, 0, d_fans.data_ptr(), n_fans, 100.0, 1081,
                                               d_out.data_ptr(), None, st.cuda_stream), "scan_batch_device")
     ms = ev_time(run, st, 100)
-    t0 = time.perf_counter()
-    vmap.ScanBatch(fans, 100.0, 1081)
-    dh = time.perf_counter() - t0
+    vmap.ScanBatch(fans, 100.0, 1081)        # first call grows the handle's device buffers
+    dhs = []
+    for _ in range(5):
+        t0 = time.perf_counter()
+        vmap.ScanBatch(fans, 100.0, 1081)
+        dhs.append(time.perf_counter() - t0)
+    dh = sorted(dhs)[2]                      # median of 5 (pageable host buffers, wall clock)
     vmap.enable_counters(True)       # rows visited and segment bytes fetched per ray (grid walk)
     run()
     cnt = vmap.read_counters()

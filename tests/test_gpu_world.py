@@ -84,6 +84,55 @@ def test_kinematic_step_parity(oracle, kind):
     assert worst_step < 1e-4
 
 
+@pytest.mark.parametrize("kind", ["ut_automata", "ut_jackal", "bwibot", "cobot"])
+def test_kinematic_step_vs_compiled_reference_models(kind):
+    """The fused step kernel against the UNMODIFIED reference models themselves
+    (ackermann/diff_drive/omnidirectional_model.cpp compiled into oracle/_ref, see
+    tests/test_ref_models.py), not the restatement: 120 free-running steps of 32 robots with
+    a drive message before every step (the reference ages commands on the wall clock, the
+    batched world in ticks: the watchdog is pinned on the CPU, tests/test_ref_models.py::
+    test_command_watchdog).  Same tolerances as above; most poses must be bit-identical."""
+    ref = oracle_lib.load_ref()
+    if ref is None or not getattr(ref, "has_models", False):
+        pytest.skip("oracle/_ref/libumrs_ref.so without the model bridge")
+    rp = umrs.default_robot(kind)
+    # the reference Ackermann model always draws its angular error from its own engine; the
+    # draws are pinned in tests/test_ref_models.py::test_ackermann_noise_draws, here they are off
+    rp.ak_angular_error_rate = 0.0
+    rp.laser.angle_increment = np.float32(0.1)
+    W = 32
+    vmap = umrs.VectorMap(lines=np.array([[-50, -50, 50, -50]], np.float32))
+    world = umrs.World(vmap, [rp], W, dt=float(DT), seed=3)
+    rng = np.random.default_rng(21)
+    poses = np.stack([rng.uniform(-5, 5, W), rng.uniform(-5, 5, W), rng.uniform(-3.1, 3.1, W)], 1).astype(np.float32)
+    world.SetPose(poses.reshape(W, 1, 3))
+    models = []
+    for w in range(W):
+        m = ref.robot_model(rp)
+        m.SetPose(poses[w])
+        models.append(m)
+    exact = total = 0
+    for step in range(120):
+        cmds = np.zeros((W, 1, 3), np.float32)
+        cmds[..., 0] = rng.uniform(-2.5, 2.5, (W, 1))
+        cmds[..., 1] = rng.uniform(-1.5, 1.5, (W, 1))
+        cmds[..., 2] = rng.uniform(-4, 4, (W, 1))
+        if step % 19 == 7:
+            cmds[::4, 0, 1] = 0.0   # exactly straight
+        world.Step(cmds)
+        gp, gv = world.GetPose()
+        for w, m in enumerate(models):
+            m.DriveCallback(cmds[w, 0])
+            m.Step(float(DT))
+            rpose, rvel = m.GetPose().astype(np.float64), m.GetVel().astype(np.float64)
+            assert np.all(np.abs(gp[w, 0] - rpose) <= 1e-4 * (1 + np.abs(rpose))), (kind, step, w, gp[w, 0], rpose)
+            assert np.all(np.abs(gv[w, 0] - rvel) <= 1e-5 * (1 + np.abs(rvel))), (kind, step, w, gv[w, 0], rvel)
+            exact += int(np.array_equal(gp[w, 0].astype(np.float32).view(np.uint32),
+                                        m.GetPose().view(np.uint32)))
+            total += 1
+    assert exact >= 0.5 * total, "only %d/%d poses bit-identical to the reference model" % (exact, total)
+
+
 @pytest.mark.parametrize("kind", ["ut_automata", "ut_jackal", "cobot"])
 def test_single_step_from_identical_state(oracle, kind):
     """One step from bit-identical state: 2e-6 * (1 + |pose|)."""
