@@ -385,6 +385,62 @@ def test_coarse_precull_keeps_every_winner(oracle):
             check_against_tierb(oracle, segs, None, fan, 30.0, n, r, i)
 
 
+@pytest.mark.parametrize("style", ["floorplan", "clutter_scales", "star", "rings"])
+def test_precull_fuzz_map_styles(oracle, style):
+    """Fuzz of the culls on maps that gather several hundred candidates per fan (the coarse
+    pre-cull is on): axis-aligned floor plans (collinear and abutting walls: ties), clutter at
+    three length scales, a star of radial walls around the pose region (all ill-conditioned from
+    the centre), concentric broken rings (occluders that cover whole chunks, gaps one or two rays
+    wide).  32 poses each, 270 and 360 degree fans; tier-B contract on every ray."""
+    rng = np.random.default_rng({"floorplan": 1, "clutter_scales": 2, "star": 3, "rings": 4}[style])
+    if style == "floorplan":
+        segs = umrs.map_cleanup(synth.floorplan_segments(1500, extent=120.0, seed=77))
+        lo, hi, rmax = 5.0, 115.0, 60.0
+    elif style == "clutter_scales":
+        parts = []
+        for n, ln in ((500, 0.05), (500, 1.0), (300, 8.0)):
+            c = rng.uniform(-40, 40, (n, 2))
+            d = rng.normal(0, 1, (n, 2))
+            d *= ln / np.linalg.norm(d, axis=1, keepdims=True)
+            parts.append(np.concatenate([c - d, c + d], 1))
+        segs = np.concatenate(parts).astype(np.float32)
+        lo, hi, rmax = -35.0, 35.0, 50.0
+    elif style == "star":
+        a = rng.uniform(-np.pi, np.pi, 900)
+        r0, r1 = rng.uniform(2.0, 30.0, 900), rng.uniform(0.2, 10.0, 900)
+        segs = np.stack([r0 * np.cos(a), r0 * np.sin(a), (r0 + r1) * np.cos(a), (r0 + r1) * np.sin(a)], 1)
+        segs = segs.astype(np.float32)
+        lo, hi, rmax = -1.5, 1.5, 45.0
+    else:
+        parts = []
+        for r in (3.0, 3.002, 6.0, 9.0, 14.0, 20.0, 27.0):
+            k = 96
+            a = np.linspace(-np.pi, np.pi, k + 1)
+            gap = rng.choice([0.0, 2e-3, 6e-3], k)           # rad, some arcs leave a slit
+            parts.append(np.stack([r * np.cos(a[:-1] + gap), r * np.sin(a[:-1] + gap),
+                                   r * np.cos(a[1:]), r * np.sin(a[1:])], 1))
+        segs = np.concatenate(parts).astype(np.float32)
+        lo, hi, rmax = -2.5, 2.5, 40.0
+    vmap = umrs.VectorMap(lines=segs)
+    m = 32
+    loc = rng.uniform(lo, hi, (m, 2))
+    if style in ("star", "rings"):
+        loc[0] = 0.0                                         # exactly the centre
+    th = rng.uniform(-np.pi, np.pi, m)
+    for half, n in ((np.float32(np.pi * 0.75), 1081), (np.float32(np.pi), 3601)):
+        fans = np.stack([loc[:, 0], loc[:, 1], th - half, th + half], 1).astype(np.float32)
+        r, i = vmap.ScanBatch(fans, rmax, n, return_index=True)
+        for k, f in enumerate(fans):
+            r_o, _ = oracle.scan_tierb(segs, None, f[:2], rmax, f[2], f[3], n)
+            fin = np.isfinite(r_o)
+            assert np.array_equal(np.isfinite(r[k]), fin), (style, k)
+            if fin.all():
+                check_against_tierb(oracle, segs, None, f, rmax, n, r[k], i[k])
+            else:
+                rel = np.abs(r[k][fin] - r_o[fin]) / np.maximum(np.abs(r_o[fin]), 1e-9)
+                assert rel.max() <= REL_TOL, (style, k)
+
+
 def test_occlusion_cull_random_clutter_many_fans(oracle):
     """Dense random clutter (short segments at all depths) from many poses: the
     cull must never remove a winner; idx compared exactly (ties certified)."""
