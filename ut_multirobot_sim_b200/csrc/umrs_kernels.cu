@@ -853,7 +853,9 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
 }
 
 // ---- scan-only kernel (umrs_predicted_scan / umrs_scan_batch) -------------------
-__global__ void __launch_bounds__(kScanThreads, UMRS_MIN_CTAS)
+// kCtas = resident fan CTAs per SM the register budget is held to (see pick_ctas below).
+template <int kCtas>
+__global__ void __launch_bounds__(kScanThreads, kCtas)
 k_scan_batch(const __grid_constant__ ScanBatchParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const SmemView sm = carve(smem_raw, p.c);
@@ -1042,7 +1044,8 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
 // CTA alone writes the "out" state (ping-pong buffers).  Order as in
 // Simulator::Run (simulator.cpp:531-541): update() first, scan from the
 // post-step pose against the post-step object lines.
-__global__ void __launch_bounds__(kScanThreads, UMRS_MIN_CTAS)
+template <int kCtas>
+__global__ void __launch_bounds__(kScanThreads, kCtas)
 k_world_step(const __grid_constant__ WorldStepParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int n_ent = p.O + p.H + p.R;
@@ -1187,21 +1190,95 @@ __global__ void k3_stats(const float* __restrict__ ranges, size_t n, double* out
 }
 
 // ---- launchers ----------------------------------------------------------------
-static size_t g_smem_configured_dev[64];
+// Register-budget variants.  The fan CTA needs 64 registers to run without spills, which
+// holds an SM to 4 resident CTAs (32 warps).  Plans with a small shared-memory footprint
+// (small maps) could seat 5 or 6; the same code compiled to 48 / 40 registers (a few
+// spilled values, -7 % / -14 % at equal occupancy) then wins on balance: 4096+ fans on a
+// 64-segment map +8.5 % with 6 CTAs, on a 256-segment map +2.7 % (same-box A/B).
+// The variant is picked per launch from the plan's shared memory and the grid size.
+struct DevLimits { int n_sm; size_t configured[3]; bool known; size_t pick_smem; int pick; bool pick_known; };
+static DevLimits g_dev[64];
 
-static cudaError_t configure_smem(size_t smem_bytes) {
+static cudaError_t dev_limits(DevLimits** out) {
   int dev = 0;
-  cudaError_t e0 = cudaGetDevice(&dev);
-  if (e0 != cudaSuccess) return e0;
-  size_t& g_smem_configured = g_smem_configured_dev[dev & 63];
-  if (smem_bytes <= g_smem_configured) return cudaSuccess;
-  cudaError_t e = cudaFuncSetAttribute(k_scan_batch, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem_bytes);
+  cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_world_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)smem_bytes);
+  DevLimits& d = g_dev[dev & 63];
+  if (!d.known) {
+    if ((e = cudaDeviceGetAttribute(&d.n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    d.known = true;
+  }
+  *out = &d;
+  return cudaSuccess;
+}
+
+// 4, 5 or 6: the most CTAs per SM the plan's shared memory seats (asked of the occupancy
+// calculator for the variant's own register count and static shared memory), but never more
+// than the grid can fill (a small batch keeps the 64-register build).
+template <int kCtas>
+static bool seats(size_t smem) {
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kCtas>, kScanThreads, smem) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return false;
+  }
+  int m = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_scan_batch<kCtas>, kScanThreads, smem) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return false;
+  }
+  return n >= kCtas && m >= kCtas;
+}
+
+static int pick_ctas(DevLimits& d, size_t smem, int fans) {
+  if (const char* v = getenv("UMRS_CTAS")) {   // experiments
+    const int f = atoi(v);
+    if (f >= UMRS_MIN_CTAS && f <= 6) return f;
+  }
+  if (!d.pick_known || d.pick_smem != smem) {
+    // a footprint above 48 KB cannot seat 5 CTAs in 228 KB: no need to ask
+    int c = UMRS_MIN_CTAS;
+    if (smem <= 48 * 1024) c = seats<6>(smem) ? 6 : (seats<5>(smem) ? 5 : UMRS_MIN_CTAS);
+    d.pick_smem = smem;
+    d.pick = c;
+    d.pick_known = true;
+  }
+  int ctas = d.pick;
+  while (ctas > UMRS_MIN_CTAS && (long long)(ctas - 1) * d.n_sm >= (long long)fans) --ctas;
+  return ctas;
+}
+
+template <typename K>
+static cudaError_t configure_smem(K kernel, DevLimits& d, int variant, size_t smem_bytes) {
+  if (smem_bytes <= d.configured[variant]) return cudaSuccess;
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+}
+
+// Both kernels of a variant share one "configured" mark: set it once both took the size.
+template <int kCtas>
+static cudaError_t configure_variant(DevLimits& d, size_t smem_bytes) {
+  const int variant = kCtas - 4;
+  cudaError_t e = configure_smem(k_scan_batch<kCtas>, d, variant, smem_bytes);
   if (e != cudaSuccess) return e;
-  g_smem_configured = smem_bytes;
+  e = configure_smem(k_world_step<kCtas>, d, variant, smem_bytes);
+  if (e != cudaSuccess) return e;
+  if (smem_bytes > d.configured[variant]) d.configured[variant] = smem_bytes;
+  return cudaSuccess;
+}
+
+template <int kCtas>
+static cudaError_t launch_scan_variant(DevLimits& d, const ScanBatchParams& p, size_t smem, cudaStream_t stream) {
+  cudaError_t e = configure_variant<kCtas>(d, smem);
+  if (e != cudaSuccess) return e;
+  k_scan_batch<kCtas><<<p.n_fans, kScanThreads, smem, stream>>>(p);
+  return cudaSuccess;
+}
+
+template <int kCtas>
+static cudaError_t launch_step_variant(DevLimits& d, const WorldStepParams& p, int fans, size_t smem, cudaStream_t stream) {
+  cudaError_t e = configure_variant<kCtas>(d, smem);
+  if (e != cudaSuccess) return e;
+  k_world_step<kCtas><<<fans, kScanThreads, smem, stream>>>(p);
   return cudaSuccess;
 }
 
@@ -1209,9 +1286,15 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) 
   if (p_in.n_fans <= 0) return cudaSuccess;
   ScanBatchParams p = p_in;
   const size_t smem = fill_smem_offsets(p.c, 0, 0);
-  cudaError_t e = configure_smem(smem);
+  DevLimits* d = nullptr;
+  cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;
-  k_scan_batch<<<p.n_fans, kScanThreads, smem, stream>>>(p);
+  switch (pick_ctas(*d, smem, p.n_fans)) {
+    case 6: e = launch_scan_variant<6>(*d, p, smem, stream); break;
+    case 5: e = launch_scan_variant<5>(*d, p, smem, stream); break;
+    default: e = launch_scan_variant<UMRS_MIN_CTAS>(*d, p, smem, stream); break;
+  }
+  if (e != cudaSuccess) return e;
   note_launch();
   return cudaGetLastError();
 }
@@ -1222,9 +1305,15 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
   WorldStepParams p = p_in;
   size_t smem = fill_smem_offsets(p.c, p.L_obj, p.O + p.H + p.R);
   if (const char* pad = getenv("UMRS_SMEM_PAD")) smem += (size_t)atoi(pad);  // occupancy experiments
-  cudaError_t e = configure_smem(smem);
+  DevLimits* d = nullptr;
+  cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;
-  k_world_step<<<fans, kScanThreads, smem, stream>>>(p);
+  switch (pick_ctas(*d, smem, fans)) {
+    case 6: e = launch_step_variant<6>(*d, p, fans, smem, stream); break;
+    case 5: e = launch_step_variant<5>(*d, p, fans, smem, stream); break;
+    default: e = launch_step_variant<UMRS_MIN_CTAS>(*d, p, fans, smem, stream); break;
+  }
+  if (e != cudaSuccess) return e;
   note_launch();
   return cudaGetLastError();
 }
