@@ -38,9 +38,6 @@
 #include "umrs_device.cuh"
 #include "umrs_internal.h"
 
-#ifndef UMRS_MIN_CTAS
-#define UMRS_MIN_CTAS 4   // resident fan CTAs per SM the register budget is held to (64 regs)
-#endif
 
 // Dev build (-DUMRS_PHASE_TIMING): thread 0 of every fan CTA adds the clock64 cycles between
 // phase boundaries to counters[8 + k] (k: 0 world phase A, 1 setup, 2 gather, 3 records,
@@ -396,7 +393,7 @@ constexpr float kPreWell = 1.2e-4f;
 constexpr float kPreMargin = 1.002f;
 constexpr float kPreSlack = 1e-3f;
 #ifndef UMRS_PRECULL_MIN   // dev builds: 1 << 30 switches S1b off
-#define UMRS_PRECULL_MIN kScanThreads
+#define UMRS_PRECULL_MIN 256
 #endif
 constexpr int kPreMinCand = UMRS_PRECULL_MIN;   // fewer candidates than threads: S2 is one trip anyway
 
@@ -853,9 +850,10 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
 }
 
 // ---- scan-only kernel (umrs_predicted_scan / umrs_scan_batch) -------------------
-// kCtas = resident fan CTAs per SM the register budget is held to (see pick_ctas below).
-template <int kCtas>
-__global__ void __launch_bounds__(kScanThreads, kCtas)
+// kThreads x kCtas = the CTA shape and the resident fan CTAs per SM the register budget is
+// held to (see the shape table at the launchers).
+template <int kThreads, int kCtas>
+__global__ void __launch_bounds__(kThreads, kCtas)
 k_scan_batch(const __grid_constant__ ScanBatchParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const SmemView sm = carve(smem_raw, p.c);
@@ -1044,8 +1042,8 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
 // CTA alone writes the "out" state (ping-pong buffers).  Order as in
 // Simulator::Run (simulator.cpp:531-541): update() first, scan from the
 // post-step pose against the post-step object lines.
-template <int kCtas>
-__global__ void __launch_bounds__(kScanThreads, kCtas)
+template <int kThreads, int kCtas>
+__global__ void __launch_bounds__(kThreads, kCtas)
 k_world_step(const __grid_constant__ WorldStepParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int n_ent = p.O + p.H + p.R;
@@ -1190,13 +1188,29 @@ __global__ void k3_stats(const float* __restrict__ ranges, size_t n, double* out
 }
 
 // ---- launchers ----------------------------------------------------------------
-// Register-budget variants.  The fan CTA needs 64 registers to run without spills, which
-// holds an SM to 4 resident CTAs (32 warps).  Plans with a small shared-memory footprint
-// (small maps) could seat 5 or 6; the same code compiled to 48 / 40 registers (a few
-// spilled values, -7 % / -14 % at equal occupancy) then wins on balance: 4096+ fans on a
-// 64-segment map +8.5 % with 6 CTAs, on a 256-segment map +2.7 % (same-box A/B).
-// The variant is picked per launch from the plan's shared memory and the grid size.
-struct DevLimits { int n_sm; size_t configured[3]; bool known; size_t pick_smem; int pick; bool pick_known; };
+// CTA shapes.  The fan code needs 64 registers to run without spills, so an SM holds 1024
+// fan threads whatever the shape; what differs is how many independent fans those threads
+// serve.  A fan's phases are separated by barriers, and it is the other resident fans that
+// fill an SM while one waits, so more and smaller CTAs win as long as shared memory seats
+// them (same-box A/B on 8192 worlds):
+//     shape            regs  64-seg map  256-seg map  needs shared memory <=
+//     256 thr x 4 CTAs  64   0.207 ms    0.229 ms     56 KB  (any plan)
+//     192 thr x 5 CTAs  64   0.191 ms    0.217 ms     44.6 KB
+//     192 thr x 6 CTAs  56   0.180 ms    0.210 ms     37 KB
+//     128 thr x 8 CTAs  64   0.159 ms    0.204 ms     27.5 KB
+// (256 threads at 48 / 40 registers for 5 / 6 CTAs: 0.198 / 0.190 ms, spills; more threads
+// per CTA, 320 / 384 at 48 / 40 registers: slower than 256 on every map.)
+// The shape is picked per launch: 128 x 8 or 192 x 6 if the plan's shared memory seats it
+// (asked of the occupancy calculator), else 256 x 4; a grid too small to fill the SMs at
+// that count keeps the widest CTA (a single scan runs fastest on 256 threads).  The
+// 1024-segment bench map (52.4 KB) stays at 256 x 4: squeezed to 44 KB (per-ray winners
+// kept in dead record fields) and run as 192 x 5 it was 2.5 % slower, so that was dropped.
+enum { kShape256x4 = 0, kShape192x5 = 1, kShape192x6 = 2, kShape128x8 = 3, kNumShapes = 4 };
+struct DevLimits {
+  int n_sm; bool known;
+  size_t configured[kNumShapes];
+  size_t pick_smem; int pick; bool pick_known;
+};
 static DevLimits g_dev[64];
 
 static cudaError_t dev_limits(DevLimits** out) {
@@ -1212,73 +1226,71 @@ static cudaError_t dev_limits(DevLimits** out) {
   return cudaSuccess;
 }
 
-// 4, 5 or 6: the most CTAs per SM the plan's shared memory seats (asked of the occupancy
-// calculator for the variant's own register count and static shared memory), but never more
-// than the grid can fill (a small batch keeps the 64-register build).
-template <int kCtas>
+template <int kThreads, int kCtas>
 static bool seats(size_t smem) {
-  int n = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kCtas>, kScanThreads, smem) != cudaSuccess) {
-    (void)cudaGetLastError();
-    return false;
-  }
-  int m = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_scan_batch<kCtas>, kScanThreads, smem) != cudaSuccess) {
+  int n = 0, m = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kThreads, kCtas>, kThreads, smem) != cudaSuccess ||
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_scan_batch<kThreads, kCtas>, kThreads, smem) != cudaSuccess) {
     (void)cudaGetLastError();
     return false;
   }
   return n >= kCtas && m >= kCtas;
 }
 
-static int pick_ctas(DevLimits& d, size_t smem, int fans) {
-  if (const char* v = getenv("UMRS_CTAS")) {   // experiments
-    const int f = atoi(v);
-    if (f >= UMRS_MIN_CTAS && f <= 6) return f;
+static int shape_ctas(int shape) {
+  return shape == kShape128x8 ? 8 : shape == kShape192x6 ? 6 : shape == kShape192x5 ? 5 : 4;
+}
+
+static int pick_shape(DevLimits& d, size_t smem, int fans) {
+  if (const char* v = getenv("UMRS_SHAPE")) {   // experiments: 0..3
+    const int f = *v ? atoi(v) : -1;
+    if (f >= 0 && f < kNumShapes) return f;
   }
   if (!d.pick_known || d.pick_smem != smem) {
-    // a footprint above 48 KB cannot seat 5 CTAs in 228 KB: no need to ask
-    int c = UMRS_MIN_CTAS;
-    if (smem <= 48 * 1024) c = seats<6>(smem) ? 6 : (seats<5>(smem) ? 5 : UMRS_MIN_CTAS);
+    int c = kShape256x4;
+    if (smem <= 48 * 1024) {   // above 48 KB not even 5 CTAs fit 228 KB: no need to ask
+      if (seats<128, 8>(smem)) c = kShape128x8;
+      else if (seats<192, 6>(smem)) c = kShape192x6;
+      // 192 x 5 (37-44.6 KB) is not picked: the gain of a smaller CTA shrinks as the
+      // candidate count grows, and at 1024 segments 192 x 5 lost 2.5 % to 256 x 4
+    }
     d.pick_smem = smem;
     d.pick = c;
     d.pick_known = true;
   }
-  int ctas = d.pick;
-  while (ctas > UMRS_MIN_CTAS && (long long)(ctas - 1) * d.n_sm >= (long long)fans) --ctas;
-  return ctas;
+  // the grid must fill every SM at (almost) the shape's CTA count for the smaller CTA to pay
+  if ((long long)fans < (long long)(shape_ctas(d.pick) - 1) * d.n_sm) return kShape256x4;
+  return d.pick;
 }
 
-template <typename K>
-static cudaError_t configure_smem(K kernel, DevLimits& d, int variant, size_t smem_bytes) {
-  if (smem_bytes <= d.configured[variant]) return cudaSuccess;
-  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-}
-
-// Both kernels of a variant share one "configured" mark: set it once both took the size.
-template <int kCtas>
-static cudaError_t configure_variant(DevLimits& d, size_t smem_bytes) {
-  const int variant = kCtas - 4;
-  cudaError_t e = configure_smem(k_scan_batch<kCtas>, d, variant, smem_bytes);
+template <int kThreads, int kCtas>
+static cudaError_t configure_shape(DevLimits& d, int shape, size_t smem_bytes) {
+  if (smem_bytes <= d.configured[shape]) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(k_scan_batch<kThreads, kCtas>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  e = configure_smem(k_world_step<kCtas>, d, variant, smem_bytes);
+  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  if (smem_bytes > d.configured[variant]) d.configured[variant] = smem_bytes;
+  d.configured[shape] = smem_bytes;
   return cudaSuccess;
 }
 
-template <int kCtas>
-static cudaError_t launch_scan_variant(DevLimits& d, const ScanBatchParams& p, size_t smem, cudaStream_t stream) {
-  cudaError_t e = configure_variant<kCtas>(d, smem);
+template <int kThreads, int kCtas>
+static cudaError_t launch_scan_shape(DevLimits& d, int shape, const ScanBatchParams& p, size_t smem,
+                                     cudaStream_t stream) {
+  cudaError_t e = configure_shape<kThreads, kCtas>(d, shape, smem);
   if (e != cudaSuccess) return e;
-  k_scan_batch<kCtas><<<p.n_fans, kScanThreads, smem, stream>>>(p);
+  k_scan_batch<kThreads, kCtas><<<p.n_fans, kThreads, smem, stream>>>(p);
   return cudaSuccess;
 }
 
-template <int kCtas>
-static cudaError_t launch_step_variant(DevLimits& d, const WorldStepParams& p, int fans, size_t smem, cudaStream_t stream) {
-  cudaError_t e = configure_variant<kCtas>(d, smem);
+template <int kThreads, int kCtas>
+static cudaError_t launch_step_shape(DevLimits& d, int shape, const WorldStepParams& p, int fans,
+                                     size_t smem, cudaStream_t stream) {
+  cudaError_t e = configure_shape<kThreads, kCtas>(d, shape, smem);
   if (e != cudaSuccess) return e;
-  k_world_step<kCtas><<<fans, kScanThreads, smem, stream>>>(p);
+  k_world_step<kThreads, kCtas><<<fans, kThreads, smem, stream>>>(p);
   return cudaSuccess;
 }
 
@@ -1289,10 +1301,12 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) 
   DevLimits* d = nullptr;
   cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;
-  switch (pick_ctas(*d, smem, p.n_fans)) {
-    case 6: e = launch_scan_variant<6>(*d, p, smem, stream); break;
-    case 5: e = launch_scan_variant<5>(*d, p, smem, stream); break;
-    default: e = launch_scan_variant<UMRS_MIN_CTAS>(*d, p, smem, stream); break;
+  const int shape = pick_shape(*d, smem, p.n_fans);
+  switch (shape) {
+    case kShape128x8: e = launch_scan_shape<128, 8>(*d, shape, p, smem, stream); break;
+    case kShape192x6: e = launch_scan_shape<192, 6>(*d, shape, p, smem, stream); break;
+    case kShape192x5: e = launch_scan_shape<192, 5>(*d, shape, p, smem, stream); break;
+    default: e = launch_scan_shape<256, 4>(*d, shape, p, smem, stream); break;
   }
   if (e != cudaSuccess) return e;
   note_launch();
@@ -1308,10 +1322,12 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
   DevLimits* d = nullptr;
   cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;
-  switch (pick_ctas(*d, smem, fans)) {
-    case 6: e = launch_step_variant<6>(*d, p, fans, smem, stream); break;
-    case 5: e = launch_step_variant<5>(*d, p, fans, smem, stream); break;
-    default: e = launch_step_variant<UMRS_MIN_CTAS>(*d, p, fans, smem, stream); break;
+  const int shape = pick_shape(*d, smem, fans);
+  switch (shape) {
+    case kShape128x8: e = launch_step_shape<128, 8>(*d, shape, p, fans, smem, stream); break;
+    case kShape192x6: e = launch_step_shape<192, 6>(*d, shape, p, fans, smem, stream); break;
+    case kShape192x5: e = launch_step_shape<192, 5>(*d, shape, p, fans, smem, stream); break;
+    default: e = launch_step_shape<256, 4>(*d, shape, p, fans, smem, stream); break;
   }
   if (e != cudaSuccess) return e;
   note_launch();
