@@ -29,16 +29,25 @@ def config1():
     segs = umrs.map_cleanup(synth.floorplan_segments(1500, 200.0, 1234))
     vmap = umrs.VectorMap(lines=segs)
     poses = synth.sample_free_poses(segs, 64, 200.0, 1234)
+    # the first calls pay one-time costs (kernel image load, shared-memory opt-in, pinned staging):
+    # reported apart, not averaged into the per-scan figure
     t0 = time.perf_counter()
-    for p in poses:
+    for p in poses[:3]:
         vmap.GetPredictedScan(p[:2], 0.4, 100.0, p[2] - d135, p[2] + d135, 1081)
-    dt = (time.perf_counter() - t0) / len(poses)
+    first3 = time.perf_counter() - t0
+    per = []
+    for p in poses:
+        t0 = time.perf_counter()
+        vmap.GetPredictedScan(p[:2], 0.4, 100.0, p[2] - d135, p[2] + d135, 1081)
+        per.append(time.perf_counter() - t0)
+    dt = float(np.median(per))
     fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - d135, poses[:, 2] + d135], 1).astype(np.float32)
     t0 = time.perf_counter()
     vmap.ScanBatch(fans, 100.0, 1081)
     db = time.perf_counter() - t0
     print(json.dumps({"config": 1, "what": "single 1081-ray scan through umrs_predicted_scan, host buffers, 1500-seg map",
-                      "ms_per_scan": dt * 1e3, "rays_per_s": 1081 / dt,
+                      "ms_per_scan": dt * 1e3, "rays_per_s": 1081 / dt, "ms_per_scan_mean": float(np.mean(per)) * 1e3,
+                      "first_3_calls_ms": first3 * 1e3,
                       "batch64_ms": db * 1e3, "batch64_rays_per_s": 64 * 1081 / db}))
 
 
