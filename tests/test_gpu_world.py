@@ -485,3 +485,33 @@ def test_pipelined_async_ticks_equal_synchronous_ticks():
     # a synchronous tick after pipelined ones is still correct
     nxt = synth.ackermann_commands(W, 1, 12)
     assert np.array_equal(worlds[1].Step(nxt).view(np.uint32), worlds[0].Step(nxt).view(np.uint32))
+
+
+@pytest.mark.parametrize("segments", [64, 1024])
+def test_cta_shapes_give_the_same_bits(monkeypatch, segments):
+    """The fan kernels exist in four CTA shapes (256x4, 192x5, 192x6, 128x8 threads x
+    CTAs per SM) and a launch picks one from its shared-memory plan and
+    grid size.  UMRS_SHAPE forces one: ranges, hit indices and poses of three noisy
+    ticks, and a scan batch over the same map, must be bit-identical in all four and
+    in the picked one (a 1024-world grid on the 64-segment map picks 128x8, the
+    1024-segment map 256x4)."""
+    W = 1200
+    runs = {}
+    for shape in ("", "0", "1", "2", "3"):
+        if shape:
+            monkeypatch.setenv("UMRS_SHAPE", shape)
+        else:
+            monkeypatch.delenv("UMRS_SHAPE", raising=False)
+        world, segs, car, vmap = _make_car_world(W, M=segments, noise=True)
+        out = []
+        for step in range(3):
+            r, i = world.Step(synth.ackermann_commands(W, 1, step), want_idx=True)
+            out += [r.view(np.uint32).copy(), i.copy()]
+        pose, vel = world.GetPose()
+        fans = world.fan_params().reshape(-1, 4)[:160]
+        rb, ib = vmap.ScanBatch(fans, 100.0, 1081, return_index=True)
+        runs[shape] = out + [pose.view(np.uint32), vel.view(np.uint32), rb.view(np.uint32), ib]
+    monkeypatch.delenv("UMRS_SHAPE", raising=False)
+    for shape in ("0", "1", "2", "3"):
+        for a, b in zip(runs[""], runs[shape]):
+            assert np.array_equal(a, b), "shape %s differs from the picked shape" % shape
