@@ -40,7 +40,7 @@ constexpr int kAgeNever = 1 << 28;
 #ifndef UMRS_SCAN_THREADS
 #define UMRS_SCAN_THREADS 256
 #endif
-constexpr int kScanThreads = UMRS_SCAN_THREADS;  // warps per fan CTA x 32
+constexpr int kScanThreads = UMRS_SCAN_THREADS;  // threads of the widest fan CTA shape (umrs_kernels.cu: launchers)
 constexpr int kMaxRays = 16384;    // per fan (bounded by the per-ray best arrays in smem)
 
 // ---- where a fan's candidate segments come from ----------------------------------

@@ -1,5 +1,6 @@
 // Scan kernels (K1 shared-memory scan, K2 uniform-grid walk) and the fused world
-// step, sm_100a.  One CTA = one ray fan (one robot's LaserScan of one world).
+// step, sm_100a.  One CTA = one ray fan (one robot's LaserScan of one world), in one of
+// four CTA shapes (threads x resident CTAs per SM) picked per launch: see the launchers.
 //
 // Replaces
 //   VectorMap::GetPredictedScan   vector_map.cpp:420-478   (per-ray fill)
@@ -19,7 +20,7 @@
 //      grid rows overlapping [loc +- range_max] for K2; then the object lines),
 //      apply the reference's AABB cull and compact the survivors' translated
 //      end points + hit index into shared memory (warp ballot + one atomic)
-//   S1b pre-cull (fans with more candidates than threads): coarse angles and
+//   S1b pre-cull (fans with more than 256 candidates): coarse angles and
 //      distances drop every candidate that lies wholly behind a wall covering
 //      its chunks, before any exact work is spent on it
 //   S2 records: one thread per survivor: lazily exact end-point angles, swap,
@@ -395,7 +396,7 @@ constexpr float kPreSlack = 1e-3f;
 #ifndef UMRS_PRECULL_MIN   // dev builds: 1 << 30 switches S1b off
 #define UMRS_PRECULL_MIN 256
 #endif
-constexpr int kPreMinCand = UMRS_PRECULL_MIN;   // fewer candidates than threads: S2 is one trip anyway
+constexpr int kPreMinCand = UMRS_PRECULL_MIN;   // fewer candidates than the widest CTA has threads: S2 is one trip anyway
 
 // atan2 to 2e-5 rad (Abramowitz & Stegun 4.4.49 on the octant-reduced ratio).
 __device__ __forceinline__ float atan2_coarse(float y, float x) {
