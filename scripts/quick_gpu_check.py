@@ -9,7 +9,8 @@ from tests import oracle_lib
 
 orc = oracle_lib.load_oracle()
 W = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
-for M in (64, 256, 1024):
+MAPS = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else [64, 256, 1024]
+for M in MAPS:
     segs = umrs.map_cleanup(synth.floorplan_segments(M, extent=200.0, seed=1234))
     vmap = umrs.VectorMap(lines=segs)
     car = umrs.default_robot("ut_automata")
