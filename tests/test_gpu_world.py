@@ -489,15 +489,15 @@ def test_pipelined_async_ticks_equal_synchronous_ticks():
 
 @pytest.mark.parametrize("segments", [64, 1024])
 def test_cta_shapes_give_the_same_bits(monkeypatch, segments):
-    """The fan kernels exist in four CTA shapes (256x4, 192x5, 192x6, 128x8 threads x
+    """The fan kernels exist in five CTA shapes (256x4, 192x5, 192x6, 128x8, 96x10 threads x
     CTAs per SM) and a launch picks one from its shared-memory plan and
     grid size.  UMRS_SHAPE forces one: ranges, hit indices and poses of three noisy
-    ticks, and a scan batch over the same map, must be bit-identical in all four and
-    in the picked one (a 1024-world grid on the 64-segment map picks 128x8, the
+    ticks, and a scan batch over the same map, must be bit-identical in all five and
+    in the picked one (a 1024-world grid on the 64-segment map picks 96x10, the
     1024-segment map 256x4)."""
     W = 1200
     runs = {}
-    for shape in ("", "0", "1", "2", "3"):
+    for shape in ("", "0", "1", "2", "3", "4"):
         if shape:
             monkeypatch.setenv("UMRS_SHAPE", shape)
         else:
@@ -512,6 +512,6 @@ def test_cta_shapes_give_the_same_bits(monkeypatch, segments):
         rb, ib = vmap.ScanBatch(fans, 100.0, 1081, return_index=True)
         runs[shape] = out + [pose.view(np.uint32), vel.view(np.uint32), rb.view(np.uint32), ib]
     monkeypatch.delenv("UMRS_SHAPE", raising=False)
-    for shape in ("0", "1", "2", "3"):
+    for shape in ("0", "1", "2", "3", "4"):
         for a, b in zip(runs[""], runs[shape]):
             assert np.array_equal(a, b), "shape %s differs from the picked shape" % shape

@@ -1199,14 +1199,15 @@ __global__ void k3_stats(const float* __restrict__ ranges, size_t n, double* out
 //     192 thr x 5 CTAs  64   0.191 ms    0.217 ms     44.6 KB
 //     192 thr x 6 CTAs  56   0.180 ms    0.210 ms     37 KB
 //     128 thr x 8 CTAs  64   0.159 ms    0.204 ms     27.5 KB
+//      96 thr x 10 CTAs 64   0.148 ms    0.209 ms     21.8 KB (used up to 18 KB)
 // (256 threads at 48 / 40 registers for 5 / 6 CTAs: 0.198 / 0.190 ms, spills; more threads
 // per CTA, 320 / 384 at 48 / 40 registers: slower than 256 on every map.)
-// The shape is picked per launch: 128 x 8 or 192 x 6 if the plan's shared memory seats it
+// The shape is picked per launch: 96 x 10, 128 x 8 or 192 x 6 if the plan's shared memory seats it
 // (asked of the occupancy calculator), else 256 x 4; a grid too small to fill the SMs at
 // that count keeps the widest CTA (a single scan runs fastest on 256 threads).  The
 // 1024-segment bench map (52.4 KB) stays at 256 x 4: squeezed to 44 KB (per-ray winners
 // kept in dead record fields) and run as 192 x 5 it was 2.5 % slower, so that was dropped.
-enum { kShape256x4 = 0, kShape192x5 = 1, kShape192x6 = 2, kShape128x8 = 3, kNumShapes = 4 };
+enum { kShape256x4 = 0, kShape192x5 = 1, kShape192x6 = 2, kShape128x8 = 3, kShape96x10 = 4, kNumShapes = 5 };
 struct DevLimits {
   int n_sm; bool known;
   size_t configured[kNumShapes];
@@ -1239,18 +1240,20 @@ static bool seats(size_t smem) {
 }
 
 static int shape_ctas(int shape) {
-  return shape == kShape128x8 ? 8 : shape == kShape192x6 ? 6 : shape == kShape192x5 ? 5 : 4;
+  return shape == kShape96x10 ? 10 : shape == kShape128x8 ? 8 : shape == kShape192x6 ? 6 : shape == kShape192x5 ? 5 : 4;
 }
 
 static int pick_shape(DevLimits& d, size_t smem, int fans) {
-  if (const char* v = getenv("UMRS_SHAPE")) {   // experiments: 0..3
+  if (const char* v = getenv("UMRS_SHAPE")) {   // experiments: 0..4
     const int f = *v ? atoi(v) : -1;
     if (f >= 0 && f < kNumShapes) return f;
   }
   if (!d.pick_known || d.pick_smem != smem) {
     int c = kShape256x4;
     if (smem <= 48 * 1024) {   // above 48 KB not even 5 CTAs fit 228 KB: no need to ask
-      if (seats<128, 8>(smem)) c = kShape128x8;
+      // 96 x 10 seats up to 21.8 KB but loses to 128 x 8 from ~19 KB (192 segments) on
+      if (smem <= 18 * 1024 && seats<96, 10>(smem)) c = kShape96x10;
+      else if (seats<128, 8>(smem)) c = kShape128x8;
       else if (seats<192, 6>(smem)) c = kShape192x6;
       // 192 x 5 (37-44.6 KB) is not picked: the gain of a smaller CTA shrinks as the
       // candidate count grows, and at 1024 segments 192 x 5 lost 2.5 % to 256 x 4
@@ -1304,6 +1307,7 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) 
   if (e != cudaSuccess) return e;
   const int shape = pick_shape(*d, smem, p.n_fans);
   switch (shape) {
+    case kShape96x10: e = launch_scan_shape<96, 10>(*d, shape, p, smem, stream); break;
     case kShape128x8: e = launch_scan_shape<128, 8>(*d, shape, p, smem, stream); break;
     case kShape192x6: e = launch_scan_shape<192, 6>(*d, shape, p, smem, stream); break;
     case kShape192x5: e = launch_scan_shape<192, 5>(*d, shape, p, smem, stream); break;
@@ -1325,6 +1329,7 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
   if (e != cudaSuccess) return e;
   const int shape = pick_shape(*d, smem, fans);
   switch (shape) {
+    case kShape96x10: e = launch_step_shape<96, 10>(*d, shape, p, fans, smem, stream); break;
     case kShape128x8: e = launch_step_shape<128, 8>(*d, shape, p, fans, smem, stream); break;
     case kShape192x6: e = launch_step_shape<192, 6>(*d, shape, p, fans, smem, stream); break;
     case kShape192x5: e = launch_step_shape<192, 5>(*d, shape, p, fans, smem, stream); break;
