@@ -821,6 +821,15 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
         precull_compact(sm);
         __syncthreads();
       }
+#ifdef UMRS_HIST   // dev build: histogram of the candidates S2 prepares per fan -> counters[8..15]
+      if (threadIdx.x == 0 && c.counters != nullptr) {
+        const int ns = pre ? sm.ctl[kCtlNSurv] : sm.ctl[kCtlNCand];
+        const int edges[7] = {192, 256, 320, 384, 448, 512, 608};
+        int b = 0;
+        while (b < 7 && ns > edges[b]) ++b;
+        atomicAdd(c.counters + 8 + b, 1ull);
+      }
+#endif
       make_records(sm, L, pre, c.counters);
       __syncthreads();
       UMRS_STAMP(c.counters, 3);
