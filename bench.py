@@ -34,6 +34,7 @@ WORLDS_PER_GPU = 8192  # BASELINE config 5: 65,536 worlds over 8 GPUs (weak scal
 EXTENT = 200.0
 FLOPS_PER_TEST = 12.0  # nominal cost of one ray-segment candidate test
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4: SMs x lanes x FMA x max SM clock
+FACTS_FILE = "r2_kernel_facts.json"   # per-launch ncu facts of k_world_step on the bench workload (scripts/ncu_facts.py)
 
 
 _JSON_FD = None
@@ -59,6 +60,8 @@ def parse():
     ap.add_argument("--cpu-sample-fans", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--no-legs", action="store_true", help="skip the config 1-4 / reference-render legs")
+    ap.add_argument("--sustained-seconds", type=float, default=2.0)
     return ap.parse_args()
 
 
@@ -73,6 +76,16 @@ def workload_name(args):
     return ("config5 shard (65,536 worlds over 8 GPUs = %d per GPU; config3 is --worlds 4096): %d worlds x 1 "
             "Ackermann x %d rays on %d GPU(s), fused step+scan, floor plan %d segs" % (
                 WORLDS_PER_GPU, w, N_RAYS, max(1, args.gpus), args.map_segments))
+
+
+def config_dict(args, n_segs):
+    """The workload, stated identically by both arms."""
+    return {"workload": workload_name(args), "worlds_per_gpu": total_worlds(args) // max(1, args.gpus),
+            "map_segments": int(n_segs), "laser_noise": True, "motion_noise": True,
+            "l2": "b200 arm: %s; reference arm: CPU, not applicable" % (
+                "not flushed" if args.no_flush else "flushed between timed steps (256 MiB memset outside the event pairs)"),
+            "timing": "b200 arm: sum of per-step CUDA-event pairs on the launch stream, max over ranks; "
+                      "reference arm: wall clock around the steps"}
 
 
 def make_inputs(args, rank, world_size):
@@ -150,69 +163,107 @@ def cpu_baseline(segs, fans, range_max, threads, budget_s):
             "kind": "reference", "seconds": dt, "fans": len(f), "passes": reps}
 
 
+def ut_automata_params():
+    """The UT-Automata car for the reference arm, from the reference's own config files
+    (config/ut_automata_config.lua:4-10, config/sim_config.lua:25-31,39-44) -- restated here so
+    that the reference arm never maps the product library."""
+    from ut_multirobot_sim_b200._lib import RobotParams      # the POD struct only; nothing is loaded
+    p = RobotParams()
+    p.model_type = 0                                         # ACKERMANN_DRIVE
+    p.ak_min_turn_radius, p.ak_max_speed, p.ak_max_accel = 0.98, 1.2, 3.0
+    p.ak_angular_error_bias, p.ak_angular_error_rate = 0.0, 0.1
+    p.car_width, p.car_length, p.rear_axle_offset, p.footprint_enabled = 0.281, 0.535, -0.162, 1
+    p.laser.loc_x, p.laser.loc_y = 0.2, 0.0
+    p.laser.angle_min, p.laser.angle_max = np.float32(np.pi * -135.0 / 180.0), np.float32(np.pi * 135.0 / 180.0)
+    p.laser.angle_increment = np.float32(np.pi * 0.25 / 180.0)
+    p.laser.range_min, p.laser.range_max, p.laser.noise_stddev = 0.4, 100.0, 0.01
+    return p
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the path on all host
-    cores -- restated Ackermann tick (oracle port; the model sources need ROS headers)
-    + the UNMODIFIED GetPredictedScan (oracle/_ref) -- on the same workload.  A step is
-    one tick of `S` worlds (S = the whole workload unless --cpu-sample-fans bounds it)."""
+    """--impl reference: the reference's own CPU implementation of the path on all host cores --
+    the map cleaned by the reference's own Load/Cleanup (vector_map.cpp:397-411), the restated
+    Ackermann tick (oracle port) + the UNMODIFIED GetPredictedScan (oracle/_ref) -- on the same
+    workload: every world of the workload, every step.  Nothing of the product is loaded."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import ctypes as C
-    import ut_multirobot_sim_b200 as umrs
-    from ut_multirobot_sim_b200 import synth
+    from ut_multirobot_sim_b200 import synth                 # pure numpy
     from tests import oracle_lib
     cores = os.cpu_count() or 1
-    segs = umrs.map_cleanup(synth.floorplan_segments(args.map_segments, extent=EXTENT, seed=1234))
     ref = oracle_lib.load_ref()
     if ref is None:
         emit(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libumrs_ref.so not built"}))
         return
     orc = oracle_lib.load_oracle()
-    car = umrs.default_robot("ut_automata")
+    rm = ref.map_from_segments(synth.floorplan_segments(args.map_segments, extent=EXTENT, seed=1234), True)
+    segs = rm.lines
+    car = ut_automata_params()
     W_total = total_worlds(args)
-    S = min(W_total, args.cpu_sample_fans or 4096)
+    S = min(W_total, args.cpu_sample_fans or W_total)
     poses = synth.sample_free_poses_fast(segs, W_total, EXTENT, seed=11)[:S]
-    rm = ref.map_from_segments(segs, False)
     states = (oracle_lib.RobotState * S)()
     for k in range(S):
         orc.lib.orc_robot_init(C.byref(states[k]), oracle_lib._fp(np.ascontiguousarray(poses[k], np.float32)))
     cmd_sets = [np.ascontiguousarray(synth.ackermann_commands(W_total, 1, s, seed=42)[:S, 0]) for s in range(8)]
     fans = np.empty((S, 4), np.float32)
 
+    # publishLaser's dropout + Gaussian noise (simulator.cpp:412-418): the normals are drawn once,
+    # outside the timed region (the reference draws them from std::default_random_engine per ray)
+    normals = np.random.default_rng(7).standard_normal(S * N_RAYS, dtype=np.float32)
+
     def one_step(step):
         orc.lib.orc_robots_tick(states, S, C.byref(car), oracle_lib._fp(cmd_sets[step % 8]),
                                 0.025, oracle_lib._fp(fans))
-        return rm.scan_batch(fans, car.laser.range_min, car.laser.range_max, N_RAYS, threads=cores)
+        out = rm.scan_batch(fans, car.laser.range_min, car.laser.range_max, N_RAYS, threads=cores)
+        orc.lib.orc_laser_postprocess(oracle_lib._fp(out), out.size, car.laser.range_max,
+                                      car.laser.noise_stddev, oracle_lib._fp(normals))
+        return out
 
     steps, warm = args.steps, args.warmup
-    # keep the whole run within a few minutes whatever --steps says
+    # keep the whole run within a few minutes whatever --steps says (the warm-up is kept as asked
+    # unless it alone would take more than a minute)
     t0 = time.perf_counter()
     one_step(0)
     per = time.perf_counter() - t0
-    steps = max(1, min(steps, int(120.0 / max(per, 1e-6))))
-    warm = max(0, min(warm, 3))
-    for s in range(warm):
+    warm_run = max(0, min(warm, int(60.0 / max(per, 1e-6))))
+    steps = max(1, min(steps, int(150.0 / max(per, 1e-6))))
+    for s in range(max(0, warm_run - 1)):     # the probe step above was warm-up step 1
         one_step(1 + s)
     t0 = time.perf_counter()
     for s in range(steps):
-        one_step(1 + warm + s)
+        one_step(warm_run + s)
     dt = time.perf_counter() - t0
     value = S * N_RAYS * steps / dt
-    sample = "%d of %d worlds per step, %d steps (requested %d), all %d host threads" % (
-        S, W_total, steps, args.steps, cores)
+    sample = "%d of %d worlds per step, %d steps (requested %d), warm-up %d (requested %d), all %d host threads" % (
+        S, W_total, steps, args.steps, warm_run, warm, cores)
     emit(json.dumps({
         "impl": "reference", "metric": "lidar_rays_per_sec", "value": value, "unit": "rays/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": dt / steps * 1e3,
+        "n_gpus": args.gpus, "steps": steps, "warmup": warm_run, "ms_per_step": dt / steps * 1e3,
         "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args), "sample": sample},
+        "config": config_dict(args, len(segs)),
+        "reference_run": {"sample": sample, "map_cleanup": "the reference's own VectorMap::Load/Cleanup (oracle/_ref)",
+                          "tick": "restated Ackermann step (oracle port), motion-noise draws zero",
+                          "scan": "unmodified GetPredictedScan, one private VectorMap per thread",
+                          "post": "dropout + noise (simulator.cpp:412-418) with pre-drawn normals"},
         "env_steps_per_sec": S * steps / dt,
         "cpu_baseline": {"value": value, "unit": "rays/s", "cores": cores, "kind": "reference",
                          "sample": sample},
         "e2e": {"value": value, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
+
+
+def source_hash():
+    """sha256 over the kernel sources the committed ncu facts describe (scripts/ncu_facts.py writes the same)."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("umrs_kernels.cu", "umrs_device.cuh"):
+        with open(os.path.join(ROOT, "ut_multirobot_sim_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
 
 
 def run_b200(args):
@@ -319,6 +370,62 @@ def run_b200(args):
     ms_e2e, h2d, d2h, _ = e2e_leg(True)
     ms_e2e = max_over_ranks(ms_e2e)
 
+    # plain pinned D2H of one step's output, timed in this run: the PCIe roofline of `e2e`
+    def pcie_peak():
+        n_bytes = W * N_RAYS * 4
+        dev = torch.empty(n_bytes, dtype=torch.uint8, device="cuda")
+        host = torch.empty(n_bytes, dtype=torch.uint8).pin_memory()
+        for _ in range(3):
+            host.copy_(dev, non_blocking=True)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 20
+        e0.record()
+        for _ in range(reps):
+            host.copy_(dev, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        return reps * n_bytes / (e0.elapsed_time(e1) * 1e-3) / 1e9
+
+    pcie_gbs = pcie_peak()
+    if world_size > 1:     # the rank with the slowest link sets the step
+        t = torch.tensor([pcie_gbs], dtype=torch.float64, device="cuda")
+        lst = [torch.zeros_like(t) for _ in range(world_size)]
+        dist.all_gather(lst, t)
+        pcie_all = [float(x.item()) for x in lst]
+    else:
+        pcie_all = [pcie_gbs]
+
+    # sustained leg: back-to-back steps for >= --sustained-seconds, no flush, clocks sampled
+    def sustained_leg():
+        secs = max(0.0, args.sustained_seconds)
+        if secs <= 0:
+            return None
+        chunk = 200
+        smp = ClockSampler(local_rank)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 0
+        with torch.cuda.stream(stream):
+            barrier()
+            smp.start()
+            t0 = time.perf_counter()
+            e0.record(stream)
+            while True:
+                for s in range(chunk):
+                    world.step_device(d_cmds[(n + s) % 8].data_ptr(), None, sp)
+                n += chunk
+                stream.synchronize()
+                if time.perf_counter() - t0 >= secs:
+                    break
+            e1.record(stream)
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        return {"steps": n, "seconds": ms * 1e-3, "ms_per_step": ms / n,
+                "value": rays_per_step * n / (ms * 1e-3), "unit": "rays/s (this rank)",
+                "l2": "not flushed (back-to-back steps)", "clocks": smp.result()}
+
+    sustained = sustained_leg()
+
     # work accounting for the roofline: one untimed step with device counters on
     world.enable_counters(True)
     world.step_device(d_cmds[0].data_ptr(), None, sp)
@@ -342,9 +449,13 @@ def run_b200(args):
     # per-launch facts of the committed `ncu --set full` capture of this workload (profiles/):
     # DRAM traffic and warp instructions executed (both properties of the launch, not of a clock)
     traffic, issue, pipes = None, None, None
+    facts_note = {"stale": False, "source": "profiles/%s" % FACTS_FILE}
     try:
-        facts = json.load(open(os.path.join(ROOT, "profiles", "r1_kernel_facts.json")))
-        if facts.get("worlds") == W and args.map_segments == 1024:
+        facts = json.load(open(os.path.join(ROOT, "profiles", FACTS_FILE)))
+        stale = facts.get("source_sha256") != source_hash()
+        if stale:
+            facts_note = {"stale": True, "why": "csrc/umrs_kernels.cu or umrs_device.cuh changed since the capture in profiles/%s" % FACTS_FILE}
+        elif facts.get("worlds") == W and args.map_segments == 1024:
             traffic = facts["dram_bytes_read"] + facts["dram_bytes_write"]
             ginst = facts["inst_executed"] / kernel_s / 1e9
             peak_ginst = 148 * 4 * 1.965            # 4 schedulers per SM, one warp instruction per clock each
@@ -353,29 +464,34 @@ def run_b200(args):
                      if k in facts}
             issue = {"achieved_ginst_per_s": ginst, "peak_ginst_per_s": peak_ginst, "frac": ginst / peak_ginst,
                      "source": "smsp__inst_executed.sum of the committed capture / live launch time; peak = 148 SM x 4 x 1.965 GHz"}
-    except Exception:
-        pass
+    except Exception as e:
+        facts_note = {"stale": True, "why": "profiles/%s missing or unreadable (%s)" % (FACTS_FILE, type(e).__name__)}
     out = {
         "metric": "lidar_rays_per_sec", "value": value, "unit": "rays/s",
         "n_gpus": world_size, "steps": K, "warmup": Wm, "ms_per_step": ms_dev / K,
         "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args), "worlds_per_gpu": W,
-                   "map_segments": int(len(segs)), "laser_noise": True, "motion_noise": True,
-                   "l2": "none" if flush is None else "flushed between timed steps (256 MiB memset outside the event pairs)",
-                   "timing": "sum of per-step CUDA-event pairs on the launch stream, max over ranks"},
+        "config": config_dict(args, len(segs)),
+        "path": "exact nearest hit per ray (tier B, SURVEY 8c): the reference's per-line formulae, minimum over all "
+                "candidates instead of its occlusion-trimmed render; the reference's own bits are the opt-in "
+                "reference render (legs.reference_render_*)",
         "env_steps_per_sec": W * world_size * K / (ms_dev * 1e-3),
         "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": h2d * world_size,
                 "d2h_bytes_per_step": d2h * world_size, "ms_per_step": ms_e2e / K,
                 "env_steps_per_sec": W * world_size * K / (ms_e2e * 1e-3),
                 "call": "umrs_world_step_async + umrs_world_wait_outputs (ticks pipelined, two pinned output buffers)",
+                "pcie": {"achieved_gbs": (d2h + h2d) / (ms_e2e / K * 1e-3) / 1e9,
+                         "peak_gbs": min(pcie_all), "peak_gbs_per_rank": pcie_all,
+                         "frac": (d2h + h2d) / (ms_e2e / K * 1e-3) / 1e9 / min(pcie_all),
+                         "peak_source": "a plain pinned device->host copy of one step's ranges (%d bytes), 20 back to back, "
+                                        "timed in this run on every rank at once; the slowest rank's link" % d2h},
                 "synchronous": {"value": total_rays * K / (ms_sync * 1e-3), "ms_per_step": ms_sync / K,
                                 "call": "umrs_world_step"}},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": FP32_PEAK_TFLOPS,
                      "unit": "TFLOP/s", "frac": achieved_tflops / FP32_PEAK_TFLOPS, "traffic": traffic,
-                     "issue": issue, "ncu_pipe_utilisation": pipes,
+                     "issue": issue, "ncu_pipe_utilisation": pipes, "ncu_facts": facts_note,
                      "brute_force_equivalent_tflops": FLOPS_PER_TEST * cnt["segs_prepared"] * N_RAYS / kernel_s / 1e12,
                      "kernel": "k_world_step", "tests_per_launch": int(tests),
                      "tests_per_ray": tests / rays_per_step,
@@ -385,9 +501,16 @@ def run_b200(args):
                      "hbm": {"achieved_gbs": alg_bytes / kernel_s / 1e9, "peak_gbs": hbm_peak,
                              "frac": alg_bytes / kernel_s / 1e9 / hbm_peak,
                              "peak_source": "measured" if "hbm_gbs" in peaks else "fallback"}},
+        "sustained": sustained,
         "stats": stats,
         "host": {"cpus_bound": None if cpus is None else len(cpus), "cpu_count": os.cpu_count()},
     }
+    if rank == 0 and world_size == 1 and not args.no_legs:
+        # BASELINE configs 1-4 and the reference render, short forms (scripts/bench_configs.py)
+        from scripts import bench_configs
+        t0 = time.perf_counter()
+        out["legs"] = bench_configs.bench_legs()
+        out["legs"]["seconds"] = time.perf_counter() - t0
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
         fans = world.fan_params().reshape(-1, 4)
         cores = os.cpu_count() or 1

@@ -1,8 +1,14 @@
-"""Dev helper: profiles/r1_kernel_facts.json (the per-launch ncu facts bench.py quotes in
-`roofline`) from an .ncu-rep of one k_world_step launch.
-usage: python scripts/ncu_facts.py gpurun_out/prof_TAG.ncu-rep > profiles/r1_kernel_facts.json"""
-import csv, io, json, subprocess, sys
+"""Dev helper: profiles/r2_kernel_facts.json (the per-launch ncu facts bench.py quotes in
+`roofline`) from an .ncu-rep of one k_world_step launch.  The facts carry a hash of the kernel
+sources they were captured from; bench.py drops them (`"stale": true`) when the sources changed.
+usage: python scripts/ncu_facts.py gpurun_out/prof_TAG.ncu-rep [summary file] > profiles/r2_kernel_facts.json"""
+import csv, hashlib, io, json, os, subprocess, sys
 rep = sys.argv[1]
+summary = sys.argv[2] if len(sys.argv) > 2 else "profiles/r2_k_world_step_ncu_full.txt"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+h = hashlib.sha256()
+for f in ("umrs_kernels.cu", "umrs_device.cuh"):
+    h.update(open(os.path.join(ROOT, "ut_multirobot_sim_b200", "csrc", f), "rb").read())
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, val = rows[0], rows[1], rows[2]
@@ -22,7 +28,8 @@ def get(name, scale_to=None):
 worlds = 8192
 facts = {
     "kernel": "k_world_step",
-    "source": "profiles/r1_k_world_step_ncu_full.txt (ncu --set full, one launch, 8192 worlds x 1081 rays, 1024-seg map)",
+    "source": "%s (ncu --set full, one launch, 8192 worlds x 1081 rays, 1024-seg map)" % summary,
+    "source_sha256": h.hexdigest(),
     "worlds": worlds,
     "rays_per_launch": worlds * 1081,
     "dram_bytes_read": int(round(get("dram__bytes_read.sum", "byte"))),

@@ -61,13 +61,28 @@ def aabb_candidates(segs, obj, loc, range_max, skip=(0, 0)):
     return idx, al[idx]
 
 
-def brute_force_f64(cands, loc, angles):
+def _wrap(x):
+    return (x + np.pi) % (2 * np.pi) - np.pi
+
+
+def spans64(cands, loc):
+    """Angle each candidate subtends from loc (float64, in [0, pi])."""
+    p = cands.astype(np.float64)
+    a0 = np.arctan2(p[:, 1] - loc[1], p[:, 0] - loc[0])
+    a1 = np.arctan2(p[:, 3] - loc[1], p[:, 2] - loc[0])
+    return np.abs(_wrap(a1 - a0))
+
+
+def brute_force_f64(cands, loc, angles, min_span=1e-4):
     """Nearest hit per ray over `cands` ([n][4] float32), float64, sidedness test.
+    Segments that subtend less than min_span rad are left out: the reference drops them before the
+    ray fill (vector_map.cpp:451, class D2 -- in BOTH tiers, it is part of the scan's definition).
     Returns (range [inf = none], candidate index [-1 = none], second-nearest range)."""
     p = cands.astype(np.float64)
     p0 = p[:, 0:2] - np.asarray(loc, np.float64)
     p1 = p[:, 2:4] - np.asarray(loc, np.float64)
     e = p1 - p0
+    seen = spans64(cands, loc) >= min_span
     a = angles.astype(np.float64)
     d = np.stack([np.cos(a), np.sin(a)], 1)                       # [R][2]
     # ray o + t d meets p0 + u e:  t = cross(p0, e) / cross(d, e),  u = cross(p0, d) / cross(d, e)
@@ -77,7 +92,7 @@ def brute_force_f64(cands, loc, angles):
     with np.errstate(divide="ignore", invalid="ignore"):
         t = ce / den
         u = cd / den
-    hit = (t > 0) & (u >= 0) & (u <= 1) & np.isfinite(t)
+    hit = (t > 0) & (u >= 0) & (u <= 1) & np.isfinite(t) & seen[None, :]
     t = np.where(hit, t, np.inf)
     order = np.argsort(t, axis=1)[:, :2]
     best = np.take_along_axis(t, order[:, :1], 1)[:, 0]
@@ -90,9 +105,6 @@ def _end_angles(seg, loc):
     s = np.asarray(seg, np.float64)
     return (np.arctan2(s[1] - loc[1], s[0] - loc[0]), np.arctan2(s[3] - loc[1], s[2] - loc[0]))
 
-
-def _wrap(x):
-    return (x + np.pi) % (2 * np.pi) - np.pi
 
 
 def covers64(seg, loc, a, tol=ANG_TOL):
@@ -195,8 +207,12 @@ class Classifier:
             elif A == W and W >= 0:
                 cls = "D6"
             elif not confirmed:
-                ends = [covers64(cands[k], loc, a)[1] for k in (W, int(i_bf[ri])) if k >= 0]
-                cls = "E" if ends and min(ends) <= ANG_TOL else None
+                # excused only at an end-point ray of either winner, or when the ray cast's winner sits on the
+                # :451 threshold (its float angles decide whether both tiers drop it)
+                both = [k for k in (W, int(i_bf[ri])) if k >= 0]
+                ends = [covers64(cands[k], loc, a)[1] for k in both]
+                on_451 = [k for k in both if abs(covers64(cands[k], loc, a)[2] - 1e-4) <= 4e-6]
+                cls = "E" if (ends and min(ends) <= ANG_TOL) else ("D2" if on_451 else None)
             elif farther:
                 mine = [k for k in range(len(rd["pieces"])) if rd["piece_parent"][k] == W]
                 live_cov = [k for k in mine if covers64(rd["pieces"][k], loc, a)[0]]
