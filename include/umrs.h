@@ -237,6 +237,8 @@ typedef struct umrs_world_desc {
                                     * O(L^2) per scan, no hit indices */
 } umrs_world_desc;
 
+/* The world keeps using the map's device buffers: the map must outlive it
+ * (umrs_map_destroy returns UMRS_ERR_INVALID while a world created from it exists). */
 int umrs_world_create(umrs_map* map, const umrs_world_desc* desc, umrs_world** out);
 int umrs_world_destroy(umrs_world* world);
 
@@ -296,6 +298,26 @@ int umrs_world_get_fan_params(umrs_world* world, float* out);
 int umrs_world_sync(umrs_world* world);
 int umrs_world_step_count(const umrs_world* world, uint64_t* steps);
 
+/* ---- checkpoint / resume -------------------------------------------------------
+ * The reference can only inject a pose (/initialpose -> SetPose, simulator.cpp:191-196).
+ * A snapshot here holds everything a BIT-REPRODUCIBLE resume needs: every robot's pose,
+ * velocity, last command, command age and the diff-drive model's double-precision
+ * velocities (diff_drive_model.h:28-31), every human's pose, (possibly swapped) start/goal
+ * and velocities (human_object.h:40-52), the static objects' poses, and the step counter
+ * that keys the Philox noise streams.  The blob is only valid for a world of the same
+ * shape (worlds, robots, humans, objects) and seed; otherwise UMRS_ERR_INVALID.
+ * Host buffers; both calls wait for the world's pending work first. */
+int umrs_world_state_size(const umrs_world* world, uint64_t* bytes);
+int umrs_world_get_state(umrs_world* world, void* blob, uint64_t capacity);
+int umrs_world_set_state(umrs_world* world, const void* blob, uint64_t bytes);
+
+/* Device-side conditions no status code could report at launch time, sticky until read:
+ * UMRS_ERR_UNSUPPORTED when a fan of the uniform-grid walk touched more grid rows than the
+ * plan sized shared memory for (the farthest rows were then NOT scanned).  The synchronous
+ * host-buffer entry points check this themselves; call these after device/async steps. */
+int umrs_map_check(umrs_map* map);
+int umrs_world_check(umrs_world* world);
+
 /* Work accounting for the roofline: candidate ray-segment tests executed and
  * candidate segments pre-processed by the scan kernel in the last step (counted
  * on the device when enabled; costs a few atomics per CTA). */
@@ -353,6 +375,17 @@ int umrs_config_laser_params(const umrs_config* cfg, umrs_laser_params* out, int
 int umrs_config_robot_params(const umrs_config* cfg, const char* robot_type,
                              umrs_robot_params* out, int32_t* n_missing);
 int umrs_config_human_params(const umrs_config* cfg, umrs_human_params* out, int32_t* n_missing);
+
+/* ---- tuning hooks (experiments and tests; process-wide; the library never reads the
+ * environment) -------------------------------------------------------------------------
+ *   "cta_shape"    -1 auto | 0..4: force one fan-CTA shape (256x4, 192x5, 192x6, 128x8, 96x10);
+ *                  a shape the plan's shared memory cannot seat is ignored
+ *   "cap"          candidate slots per pass, 32..4064 (0 = default 1536)
+ *   "grid_from"    map size from which the uniform-grid walk is picked (0 = default 4096)
+ *   "step_slices"  world slices of a host-buffer tick, 1..15 (0 = auto)
+ * UMRS_ERR_INVALID for an unknown key or a value out of range. */
+int umrs_tuning_set(const char* key, int32_t value);
+int umrs_tuning_get(const char* key, int32_t* value);
 
 /* Philox4x32-10 as used for the noise (host restatement for tests):
  * counter {c0,c1,c2,c3}, key {k0,k1} -> 4 words. */

@@ -1,6 +1,7 @@
 #!/bin/bash
 # Dev helper: GPU parity tests + same-box A/B timings of kernel variants.
-# usage: scripts/gpu_ab.sh "VAR=val ..." "VAR=val ..."   (one quoted env set per variant)
+# usage: scripts/gpu_ab.sh "VAR=val ..." "VAR=val ..."   (one quoted env set per variant: UMRS_LIB=build/x.so,
+# UMRS_TUNE_CTA_SHAPE=3, UMRS_TUNE_CAP=..., see ut_multirobot_sim_b200/_lib.py)
 timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/pytest_gpu.log
 i=0
 for V in "$@"; do

@@ -206,30 +206,33 @@ def test_large_map_grid_walk(oracle):
 
 
 @pytest.mark.parametrize("kernel", [0, 1], ids=["k1_smem", "k2_grid"])
-def test_multipass_when_candidates_exceed_the_slots(oracle, monkeypatch, kernel):
-    """UMRS_CAP bounds the shared-memory candidate slots per pass: with 96 slots a
+def test_multipass_when_candidates_exceed_the_slots(oracle, kernel):
+    """The "cap" tuning hook bounds the shared-memory candidate slots per pass: with 96 slots a
     1024-segment fan takes ~11 passes; results (incl. ties across passes and the
     object lines, which live in the last source row) must not change."""
     lib = _lib.load()
-    monkeypatch.setenv("UMRS_CAP", "96")
     g = _load(os.path.join(HERE, "golden", "clutter_objects.npz"))
     n, rmax = int(g["num_rays"]), float(g["range_max"])
     vmap = umrs.VectorMap(lines=g["segs"])
     vmap.object_lines = g["obj"]
     _lib.check(lib.umrs_map_set_scan_kernel(vmap._h, kernel), "set_scan_kernel")
-    r, i = vmap.ScanBatch(g["fans"], rmax, n, return_index=True)
+    with _lib.tuning(cap=96):
+        r, i = vmap.ScanBatch(g["fans"], rmax, n, return_index=True)
     for k, f in enumerate(g["fans"]):
         check_against_tierb(oracle, g["segs"], g["obj"], f, rmax, n, r[k], i[k])
-    monkeypatch.delenv("UMRS_CAP")
     r1, i1 = vmap.ScanBatch(g["fans"], rmax, n, return_index=True)
     assert np.array_equal(r.view(np.uint32), r1.view(np.uint32)) and np.array_equal(i, i1)
     # duplicates split across passes still resolve to the lowest index
-    monkeypatch.setenv("UMRS_CAP", "32")
-    segs = np.array([[5, -3, 5, 3]] * 70 + [[7, -3, 7, 3]], np.float32)
-    vm2 = umrs.VectorMap(lines=segs)
-    _lib.check(lib.umrs_map_set_scan_kernel(vm2._h, kernel), "set_scan_kernel")
-    r2, i2 = vm2.GetPredictedScan((0, 0), 0.4, 50.0, -0.4, 0.4, 101, return_index=True)
+    with _lib.tuning(cap=32):
+        segs = np.array([[5, -3, 5, 3]] * 70 + [[7, -3, 7, 3]], np.float32)
+        vm2 = umrs.VectorMap(lines=segs)
+        _lib.check(lib.umrs_map_set_scan_kernel(vm2._h, kernel), "set_scan_kernel")
+        r2, i2 = vm2.GetPredictedScan((0, 0), 0.4, 50.0, -0.4, 0.4, 101, return_index=True)
     assert np.all(i2 == 0)
+    # the hooks validate their arguments and never read the environment
+    assert lib.umrs_tuning_set(b"cap", 7) == _lib.ERR_INVALID
+    assert lib.umrs_tuning_set(b"cta_shape", 9) == _lib.ERR_INVALID
+    assert lib.umrs_tuning_set(b"no_such_key", 1) == _lib.ERR_INVALID
 
 
 def test_grid_kernel_with_long_segments_and_far_poses(oracle):

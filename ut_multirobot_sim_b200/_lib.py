@@ -149,7 +149,18 @@ SIGNATURES = {
     "umrs_config_human_params": (C.c_int, [_P, C.POINTER(HumanParams), _I]),
     "umrs_philox4x32": (None, [C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
                                C.POINTER(C.c_uint32)]),
+    "umrs_world_state_size": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
+    "umrs_world_get_state": (C.c_int, [_P, _P, C.c_uint64]),
+    "umrs_world_set_state": (C.c_int, [_P, _P, C.c_uint64]),
+    "umrs_map_check": (C.c_int, [_P]),
+    "umrs_world_check": (C.c_int, [_P]),
+    "umrs_tuning_set": (C.c_int, [C.c_char_p, C.c_int32]),
+    "umrs_tuning_get": (C.c_int, [C.c_char_p, _I]),
 }
+
+# Dev convenience for A/B scripts: UMRS_TUNE_<KEY>=<int> in the environment is handed to
+# umrs_tuning_set once, when the library is loaded (the library itself never reads the environment).
+TUNING_KEYS = ("cta_shape", "cap", "grid_from", "step_slices")
 
 _lib = None
 
@@ -169,7 +180,33 @@ def load():
         fn.restype = res
         fn.argtypes = args
     _lib = lib
+    for key in TUNING_KEYS:
+        v = os.environ.get("UMRS_TUNE_" + key.upper())
+        if v not in (None, ""):
+            check(lib.umrs_tuning_set(key.encode(), int(v)), "umrs_tuning_set(%s)" % key)
     return lib
+
+
+class tuning:
+    """with tuning(cta_shape=3, cap=96): ...   -- sets the hooks, restores the previous values."""
+
+    def __init__(self, **kv):
+        self.kv, self.old = kv, {}
+
+    def __enter__(self):
+        lib = load()
+        for k, v in self.kv.items():
+            o = C.c_int32(0)
+            check(lib.umrs_tuning_get(k.encode(), C.byref(o)), "umrs_tuning_get")
+            self.old[k] = o.value
+            check(lib.umrs_tuning_set(k.encode(), int(v)), "umrs_tuning_set(%s=%s)" % (k, v))
+        return self
+
+    def __exit__(self, *exc):
+        lib = load()
+        for k, v in self.old.items():
+            lib.umrs_tuning_set(k.encode(), int(v))
+        return False
 
 
 class UmrsError(RuntimeError):

@@ -288,6 +288,22 @@ class World:
                 "passes": ex[3], "tie_sweeps": ex[4], "spilled_entries": ex[5], "sweep_all_fans": ex[6],
                 "source_segments": ex[7] & ((1 << 40) - 1), "source_rows": ex[7] >> 40}
 
+    def get_state(self):
+        """Snapshot for a bit-reproducible resume (umrs_world_get_state): bytes."""
+        n = C.c_uint64(0)
+        check(self._lib.umrs_world_state_size(self._h, C.byref(n)), "umrs_world_state_size")
+        buf = (C.c_ubyte * n.value)()
+        check(self._lib.umrs_world_get_state(self._h, buf, n.value), "umrs_world_get_state")
+        return bytes(buf)
+
+    def set_state(self, blob):
+        buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        check(self._lib.umrs_world_set_state(self._h, buf, len(blob)), "umrs_world_set_state")
+
+    def check(self):
+        """Raises if a device-side condition was flagged since the last check (umrs_world_check)."""
+        check(self._lib.umrs_world_check(self._h), "umrs_world_check")
+
     def phase_cycles(self):
         """Dev builds (-DUMRS_PHASE_TIMING): summed critical-path cycles per phase; zeros otherwise."""
         ex = (C.c_uint64 * 8)()

@@ -22,6 +22,7 @@ namespace umrs {
 
 static thread_local std::string g_last_cuda_error;
 static std::atomic<uint64_t> g_launches{0};
+Tuning g_tuning;
 
 void note_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
@@ -83,6 +84,8 @@ struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; 
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
 void capi_map_segments(const umrs_map* m, const float4** segs_map_order, int32_t* n);
+void capi_map_retain(umrs_map* m, int delta);
+int capi_read_flags(uint32_t* d_flags);
 }  // namespace umrs
 
 // ================================== map ==========================================
@@ -108,6 +111,8 @@ struct umrs_map {
   // work accounting of the scan entry points (umrs_map_enable_counters)
   unsigned long long* d_counters = nullptr;
   bool counters_on = false;
+  uint32_t* d_flags = nullptr;     // sticky device-side conditions (kFlagRowsTruncated)
+  std::atomic<int> n_worlds{0};    // worlds created from this map (they use its device buffers)
   // pinned staging for small host-buffer scans (a pageable cudaMemcpyAsync stages and
   // synchronises inside the driver; a single LaserScan is 4 KB)
   float* h_stage = nullptr;        // [kStageFloats] outputs, then kStageIn floats of inputs
@@ -199,6 +204,8 @@ static int map_from_clean(const float* segs, int32_t n, umrs_map** out) {
   if (e == cudaSuccess && n > 0)
     e = cudaMemcpy(m->d_segs, segs, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = build_grid(m);
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&m->d_flags), sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMemset(m->d_flags, 0, sizeof(uint32_t));
   if (e != cudaSuccess) {
     int rc = cuda_fail(e, "umrs_map_create");
     umrs_map_destroy(m);
@@ -215,19 +222,17 @@ void capi_map_segments(const umrs_map* m, const float4** segs_map_order, int32_t
   *n = m->n;
 }
 
+void capi_map_retain(umrs_map* m, int delta) { m->n_worlds.fetch_add(delta); }
+
 // Picks the kernel variant and the shared-memory plan for a launch against map m.
 //   K1 (kernel 0): every fan streams the whole map;  K2 (kernel 1): grid rows.
 // auto: K2 from 4096 map segments up.  cap = candidate slots per pass.
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
-}
 
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out) {
   ScanPlan pl;
   memset(&pl, 0, sizeof(pl));
-  const bool grid = m->force_kernel == 1 || (m->force_kernel < 0 && m->n >= env_int("UMRS_GRID_FROM", 4096));
+  const bool grid = m->force_kernel == 1 || (m->force_kernel < 0 && m->n >= (g_tuning.grid_from > 0 ? g_tuning.grid_from : 4096));
   pl.kernel = grid ? 1 : 0;
   pl.smem_optin = m->smem_optin;
   MapSource& s = pl.src;
@@ -238,8 +243,11 @@ int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t ma
     s.cell_start = m->d_cell_start; s.gx = m->gx; s.gy = m->gy;
     s.x0 = m->gx0; s.y0 = m->gy0; s.cell = m->cell; s.inv_cell = m->inv_cell;
     s.hmax_x = m->hmax_x; s.hmax_y = m->hmax_y;
-    const double reach = 2.0 * ((double)range_max * 1.00002 + (double)m->hmax_y + 2e-3 * m->cell) ;
-    double rows = floor(reach * (double)m->inv_cell) + 3.0;
+    // rows a fan's query box [ly +- (range_max + margin)] can overlap: the kernel's own margin
+    // (grid_margin, umrs_internal.h) at the largest |ly| for which the box still meets the grid
+    const float y_far = std::max(fabsf(m->gy0), fabsf(m->gy0 + (float)m->gy * m->cell)) + 2.0f * fabsf(range_max);
+    const double reach = 2.0 * ((double)range_max + (double)grid_margin(m->hmax_y, m->cell, y_far, range_max));
+    double rows = floor(reach * (double)m->inv_cell * 1.00001) + 3.0;
     if (!(rows < (double)m->gy + 1.0)) rows = (double)m->gy + 1.0;  // also NaN / inf range_max
     pl.max_rows = (int32_t)rows + 3;  // + long-segment tail + object row + spare
   } else {
@@ -248,7 +256,7 @@ int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t ma
     pl.max_rows = 3;
   }
   // bucket entries are 16 * slot in 16 bits -> at most 4064 slots per pass
-  const int cap_max = std::max(32, std::min(env_int("UMRS_CAP", 1536), 4064));
+  const int cap_max = std::max(32, std::min(g_tuning.cap > 0 ? g_tuning.cap : 1536, 4064));
   int64_t need = (int64_t)m->n + n_obj;
   int32_t cap = (int32_t)std::min<int64_t>(std::max<int64_t>(need, 32), cap_max);
   cap = (cap + 31) & ~31;
@@ -315,6 +323,12 @@ int umrs_map_load_file(const char* path, umrs_map** out) {
 
 int umrs_map_destroy(umrs_map* m) {
   if (m == NULL) return UMRS_OK;
+  if (m->n_worlds.load() > 0) {
+    g_last_cuda_error = "umrs_map_destroy: worlds created from this map still exist";
+    return UMRS_ERR_INVALID;
+  }
+  if (m->stream) cudaStreamSynchronize(m->stream);
+  if (m->d_flags) cudaFree(m->d_flags);
   if (m->d_segs) cudaFree(m->d_segs);
   if (m->d_sorted) cudaFree(m->d_sorted);
   if (m->d_orig) cudaFree(m->d_orig);
@@ -374,6 +388,47 @@ int umrs_map_read_counters(umrs_map* m, uint64_t out8[8]) {
   return UMRS_OK;
 }
 
+static int read_flags(uint32_t* d_flags) {
+  if (d_flags == nullptr) return UMRS_OK;
+  uint32_t f = 0;
+  UMRS_CUDA(cudaMemcpy(&f, d_flags, sizeof(f), cudaMemcpyDeviceToHost));
+  if (f == 0) return UMRS_OK;
+  UMRS_CUDA(cudaMemset(d_flags, 0, sizeof(f)));
+  if (f & kFlagRowsTruncated) {
+    g_last_cuda_error = "a fan touched more grid rows than the plan sized shared memory for (far rows not scanned)";
+    return UMRS_ERR_UNSUPPORTED;
+  }
+  return UMRS_OK;
+}
+
+int umrs_map_check(umrs_map* m) {
+  if (m == NULL) return UMRS_ERR_INVALID;
+  UMRS_CUDA(cudaDeviceSynchronize());
+  return read_flags(m->d_flags);
+}
+
+int umrs_tuning_set(const char* key, int32_t value) {
+  if (key == NULL) return UMRS_ERR_INVALID;
+  const std::string k(key);
+  if (k == "cta_shape") { if (value < -1 || value > 4) return UMRS_ERR_INVALID; g_tuning.cta_shape = value; }
+  else if (k == "cap") { if (value != 0 && (value < 32 || value > 4064)) return UMRS_ERR_INVALID; g_tuning.cap = value; }
+  else if (k == "grid_from") { if (value < 0) return UMRS_ERR_INVALID; g_tuning.grid_from = value; }
+  else if (k == "step_slices") { if (value < 0 || value > 15) return UMRS_ERR_INVALID; g_tuning.step_slices = value; }
+  else return UMRS_ERR_INVALID;
+  return UMRS_OK;
+}
+
+int umrs_tuning_get(const char* key, int32_t* value) {
+  if (key == NULL || value == NULL) return UMRS_ERR_INVALID;
+  const std::string k(key);
+  if (k == "cta_shape") *value = g_tuning.cta_shape;
+  else if (k == "cap") *value = g_tuning.cap;
+  else if (k == "grid_from") *value = g_tuning.grid_from;
+  else if (k == "step_slices") *value = g_tuning.step_slices;
+  else return UMRS_ERR_INVALID;
+  return UMRS_OK;
+}
+
 int umrs_scan_batch_device(umrs_map* m, const float* obj_segs_dev, int32_t n_obj,
                            const float* fans_dev, int32_t n_fans, float range_max,
                            int32_t num_rays, float* ranges_dev, int32_t* hit_idx_dev,
@@ -398,6 +453,7 @@ int umrs_scan_batch_device(umrs_map* m, const float* obj_segs_dev, int32_t n_obj
   p.c.ranges = ranges_dev;
   p.c.hit_idx = hit_idx_dev;
   p.c.counters = nullptr;
+  p.c.flags = m->d_flags;
   if (m->counters_on && m->d_counters != nullptr) {
     p.c.counters = m->d_counters;
     UMRS_CUDA(cudaMemsetAsync(m->d_counters, 0, sizeof(unsigned long long) * kNumCounters,
@@ -470,6 +526,9 @@ int umrs_scan_batch(umrs_map* m, const float* obj_segs_xyxy, int32_t n_obj,
     memcpy(ranges_out, dst_r, sizeof(float) * n_out);
     if (hit_idx_out) memcpy(hit_idx_out, dst_i, sizeof(int32_t) * n_out);
   }
+  // only the grid walk can raise a device-side condition (row table overflow)
+  if (m->force_kernel == 1 || (m->force_kernel < 0 && m->n >= (g_tuning.grid_from > 0 ? g_tuning.grid_from : 4096)))
+    return read_flags(m->d_flags);
   return UMRS_OK;
 }
 
@@ -553,3 +612,7 @@ int umrs_predicted_scan(umrs_map* m, const float* obj_segs_xyxy, int32_t n_obj,
 }
 
 }  // extern "C"
+
+namespace umrs {
+int capi_read_flags(uint32_t* d_flags) { return read_flags(d_flags); }
+}  // namespace umrs

@@ -64,6 +64,24 @@ struct MapSource {
 };
 
 constexpr int kNumCounters = 16;
+constexpr uint32_t kFlagRowsTruncated = 1u;   // build_rows ran out of row slots: far grid rows not scanned
+
+// Margin by which the grid walk widens its query box (K2): the largest midpoint-to-endpoint
+// offset of a binned segment, plus a term that dominates every float rounding in the cell
+// computation and in the host binning.  ONE definition for the kernel (build_rows) and for the
+// host's bound on the rows a fan can touch (capi_scan_plan).
+__host__ __device__ inline float grid_margin(float hmax, float cell, float abs_l, float range_max) {
+  return hmax + 1e-3f * cell + 1e-5f * (abs_l + range_max);
+}
+
+// Process-wide tuning hooks (umrs_tuning_set); 0 / -1 = default.
+struct Tuning {
+  int cta_shape = -1;
+  int cap = 0;
+  int grid_from = 0;
+  int step_slices = 0;
+};
+extern Tuning g_tuning;
 
 struct ScanCommon {
   MapSource src;
@@ -71,6 +89,7 @@ struct ScanCommon {
   int32_t* hit_idx;              // nullable, same shape
   unsigned long long* counters;  // nullable: [kNumCounters] {tests, segs_prepared, chunk_seg_pairs, passes,
                                  // tie sweeps, spilled, sweep-all fans, -, 8 phase-cycle sums (dev builds)}
+  uint32_t* flags;               // nullable: sticky device-side conditions (kFlagRowsTruncated)
   int32_t cap;                   // candidate slots per pass (smem sizing)
   int32_t max_rows;              // source rows a fan can touch (smem sizing)
   int32_t max_rays;              // largest num_rays of any fan of the launch (smem sizing)

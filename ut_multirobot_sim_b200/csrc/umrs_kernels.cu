@@ -36,6 +36,8 @@
 //      stores of ranges / hit indices
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "umrs_device.cuh"
 #include "umrs_internal.h"
 
@@ -173,7 +175,7 @@ struct PostProcess {
 // [row_v0[r], row_v0[r+1]) = source [row_s0[r], ...).  The LAST row is always the
 // object-line row (possibly empty).  Written by thread 0.
 __device__ void build_rows(const SmemView& sm, const MapSource& src, const Fan& fan, int n_obj,
-                           int max_rows) {
+                           int max_rows, uint32_t* flags) {
   int r = 0, v = 0;
   if (src.gx == 0) {
     sm.row_v0[r] = v; sm.row_s0[r] = 0; v += src.n; ++r;
@@ -181,8 +183,8 @@ __device__ void build_rows(const SmemView& sm, const MapSource& src, const Fan& 
     // cells whose binned segments (by midpoint) can pass the AABB cull: widen the
     // query box by the largest midpoint-to-endpoint offset, plus a margin that
     // dominates every float rounding in this computation and in the host binning
-    const float mx = src.hmax_x + 1e-3f * src.cell + 1e-5f * (fabsf(fan.lx) + fan.range_max);
-    const float my = src.hmax_y + 1e-3f * src.cell + 1e-5f * (fabsf(fan.ly) + fan.range_max);
+    const float mx = grid_margin(src.hmax_x, src.cell, fabsf(fan.lx), fan.range_max);
+    const float my = grid_margin(src.hmax_y, src.cell, fabsf(fan.ly), fan.range_max);
     const float fx0 = ((fan.lx - fan.range_max - mx) - src.x0) * src.inv_cell;
     const float fx1 = ((fan.lx + fan.range_max + mx) - src.x0) * src.inv_cell;
     const float fy0 = ((fan.ly - fan.range_max - my) - src.y0) * src.inv_cell;
@@ -194,10 +196,15 @@ __device__ void build_rows(const SmemView& sm, const MapSource& src, const Fan& 
     int cy1 = fy1 >= 0.f ? (fy1 < (float)src.gy ? (int)fy1 : src.gy - 1) : -1;
     if (!(fx0 == fx0) || !(fx1 == fx1) || !(fy0 == fy0) || !(fy1 == fy1)) cx1 = -1;
     if (cx0 <= cx1) {
-      for (int cy = cy0; cy <= cy1 && r < max_rows - 2; ++cy) {
+      for (int cy = cy0; cy <= cy1; ++cy) {
         const int s0 = __ldg(src.cell_start + cy * src.gx + cx0);
         const int s1 = __ldg(src.cell_start + cy * src.gx + cx1 + 1);
-        if (s1 > s0) { sm.row_v0[r] = v; sm.row_s0[r] = s0; v += s1 - s0; ++r; }
+        if (s1 <= s0) continue;
+        if (r >= max_rows - 2) {   // cannot happen while the host bound (capi_scan_plan) holds; never silent
+          if (flags != nullptr) atomicOr(flags, kFlagRowsTruncated);
+          break;
+        }
+        sm.row_v0[r] = v; sm.row_s0[r] = s0; v += s1 - s0; ++r;
       }
     }
     // always-visited tail: segments longer than two cells
@@ -779,7 +786,7 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
   const Lattice L = make_lattice(fan.amin, fan.amax, fan.num_rays);
   const int n_chunks = (fan.num_rays + 31) >> 5;
   const int K = bucket_capacity(c.cap, (c.max_rays + 31) >> 5, n_chunks);
-  if (threadIdx.x == 0) build_rows(sm, c.src, fan, n_obj, c.max_rows);
+  if (threadIdx.x == 0) build_rows(sm, c.src, fan, n_obj, c.max_rows, c.flags);
   if (threadIdx.x >= 32 && threadIdx.x < 36) sm.ctl[threadIdx.x - 32] = 0;
   if (threadIdx.x == 36) sm.ctl[kCtlNSurv] = 0;
   if (threadIdx.x == 64) {
@@ -1223,6 +1230,7 @@ struct DevLimits {
   size_t pick_smem; int pick; bool pick_known;
 };
 static DevLimits g_dev[64];
+static std::mutex g_dev_mutex;
 
 static cudaError_t dev_limits(DevLimits** out) {
   int dev = 0;
@@ -1253,10 +1261,10 @@ static int shape_ctas(int shape) {
 }
 
 static int pick_shape(DevLimits& d, size_t smem, int fans) {
-  if (const char* v = getenv("UMRS_SHAPE")) {   // experiments: 0..4
-    const int f = *v ? atoi(v) : -1;
-    if (f >= 0 && f < kNumShapes) return f;
-  }
+  // umrs_tuning_set("cta_shape"): experiments and tests.  Every shape runs any plan that fits the
+  // opt-in shared memory at all (a plan too big to seat kCtas CTAs just runs at lower occupancy).
+  const int forced = g_tuning.cta_shape;
+  if (forced >= 0 && forced < kNumShapes) return forced;
   if (!d.pick_known || d.pick_smem != smem) {
     int c = kShape256x4;
     if (smem <= 48 * 1024) {   // above 48 KB not even 5 CTAs fit 228 KB: no need to ask
@@ -1311,6 +1319,7 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) 
   if (p_in.n_fans <= 0) return cudaSuccess;
   ScanBatchParams p = p_in;
   const size_t smem = fill_smem_offsets(p.c, 0, 0);
+  std::lock_guard<std::mutex> lock(g_dev_mutex);
   DevLimits* d = nullptr;
   cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;
@@ -1331,8 +1340,8 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
   const int fans = p_in.world_count * p_in.R;
   if (fans <= 0) return cudaSuccess;
   WorldStepParams p = p_in;
-  size_t smem = fill_smem_offsets(p.c, p.L_obj, p.O + p.H + p.R);
-  if (const char* pad = getenv("UMRS_SMEM_PAD")) smem += (size_t)atoi(pad);  // occupancy experiments
+  const size_t smem = fill_smem_offsets(p.c, p.L_obj, p.O + p.H + p.R);
+  std::lock_guard<std::mutex> lock(g_dev_mutex);   // the per-device shape cache is shared by all handles
   DevLimits* d = nullptr;
   cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;

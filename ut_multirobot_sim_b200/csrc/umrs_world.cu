@@ -24,6 +24,8 @@ struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; 
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
 void capi_map_segments(const umrs_map* m, const float4** segs_map_order, int32_t* n);
+void capi_map_retain(umrs_map* m, int delta);
+int capi_read_flags(uint32_t* d_flags);
 }  // namespace umrs
 
 #define UMRS_CUDA(call)                                          \
@@ -36,6 +38,7 @@ constexpr int kMaxSlices = 16;
 
 struct umrs_world {
   umrs_world_desc desc;
+  umrs_map* map = nullptr;   // retained: the plan points into its device buffers
   std::vector<umrs_robot_params> robots;
   std::vector<umrs_human_params> humans;
   ScanPlan plan;  // kernel variant + shared-memory plan, fixed at creation
@@ -52,8 +55,10 @@ struct umrs_world {
   // and whole-tick completion, both recorded on the copy stream
   cudaEvent_t copy_done[kMaxSlices] = {};
   cudaEvent_t tick_done[4] = {};
+  cudaEvent_t kernels_done = nullptr;   // all slice kernels of a pipelined tick
   uint64_t async_ticks = 0;
-  bool async_pending = false;
+  bool async_pending = false;     // device->host copies of a pipelined tick may still be running ...
+  int pending_slices = 0;         // ... in this many slices (copy_done[0 .. pending_slices))
   uint64_t step = 0;
   int cur = 0;  // index of the "in" state buffer
   // device
@@ -81,6 +86,7 @@ struct umrs_world {
   float* d_render_c = nullptr;
   bool counters_on = false;
   double* d_stats = nullptr;
+  uint32_t* d_flags = nullptr;   // sticky device-side conditions (kFlagRowsTruncated)
 };
 
 template <typename T>
@@ -92,6 +98,12 @@ extern "C" {
 
 int umrs_world_destroy(umrs_world* w) {
   if (w == NULL) return UMRS_OK;
+  // the caller's (pinned) output buffers may still be copy targets
+  if (w->stream) cudaStreamSynchronize(w->stream);
+  if (w->copy_stream) cudaStreamSynchronize(w->copy_stream);
+  if (w->map) capi_map_retain(w->map, -1);
+  if (w->d_flags) cudaFree(w->d_flags);
+  if (w->kernels_done) cudaEventDestroy(w->kernels_done);
   void* ptrs[] = {w->d_robots, w->d_humans, w->d_tmpl, w->d_line_ent, w->d_ent_off,
                   w->d_ray_off, w->d_num_rays, w->d_rs[0], w->d_rs[1], w->d_hs[0],
                   w->d_hs[1], w->d_static, w->d_cmds, w->d_mask, w->d_ranges, w->d_idx,
@@ -128,6 +140,8 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   w->desc.robots = nullptr;
   w->desc.humans = nullptr;
   capi_map_segments(map, &w->map_segs_in_map_order, &w->n_map);
+  w->map = map;
+  capi_map_retain(map, +1);
 
   // ---- object-line roster: [statics][humans][robot bodies] ---------------------
   std::vector<float> tmpl;      // xyxy per world-line
@@ -232,6 +246,9 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (ok()) e = dalloc(&w->d_pose, WR * 3);
   if (ok()) e = dalloc(&w->d_counters, (size_t)kNumCounters);
   if (ok()) e = dalloc(&w->d_stats, (size_t)4);
+  if (ok()) e = dalloc(&w->d_flags, (size_t)1);
+  if (ok()) e = cudaMemset(w->d_flags, 0, sizeof(uint32_t));
+  if (ok()) e = cudaEventCreateWithFlags(&w->kernels_done, cudaEventDisableTiming);
   if (ok()) e = cudaMemcpy(w->d_robots, w->robots.data(), sizeof(umrs_robot_params) * w->R, cudaMemcpyHostToDevice);
   if (ok() && w->H) e = cudaMemcpy(w->d_humans, w->humans.data(), sizeof(umrs_human_params) * w->H, cudaMemcpyHostToDevice);
   if (ok() && w->L_obj) e = cudaMemcpy(w->d_tmpl, tmpl.data(), sizeof(float4) * w->L_obj, cudaMemcpyHostToDevice);
@@ -385,6 +402,7 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   p.c.ranges = w->d_ranges;
   p.c.hit_idx = w->d_idx;
   p.c.counters = w->counters_on ? w->d_counters : nullptr;
+  p.c.flags = w->d_flags;
   p.W = w->W; p.R = w->R; p.H = w->H; p.O = w->O;
   p.world_first = first; p.world_count = count;
   p.robots = w->d_robots;
@@ -458,7 +476,12 @@ extern "C" {
 int umrs_world_step_device(umrs_world* w, const float* cmds_dev, const uint8_t* mask_dev,
                            void* stream) {
   if (w == NULL) return UMRS_ERR_INVALID;
-  return world_launch(w, cmds_dev, mask_dev, stream ? (cudaStream_t)stream : w->stream, 0, w->W, true);
+  cudaStream_t st = stream ? (cudaStream_t)stream : w->stream;
+  // this launch overwrites d_ranges / d_idx: every device->host copy a pipelined host-buffer tick
+  // still has in flight must be done first (the events stay recorded; the flag is cleared by a wait)
+  if (w->async_pending)
+    for (int s = 0; s < w->pending_slices; ++s) UMRS_CUDA(cudaStreamWaitEvent(st, w->copy_done[s], 0));
+  return world_launch(w, cmds_dev, mask_dev, st, 0, w->W, true);
 }
 
 }  // extern "C"
@@ -490,14 +513,20 @@ static int step_enqueue(umrs_world* w, const float* cmds, const uint8_t* cmd_mas
   }
   int n_slices = 1;
   if (ranges_out != NULL && w->W >= 1024) n_slices = pipelined ? 4 : 8;
-  if (const char* e = getenv("UMRS_STEP_SLICES")) n_slices = atoi(e) > 0 ? atoi(e) : 1;
+  if (g_tuning.step_slices > 0) n_slices = g_tuning.step_slices;   // umrs_tuning_set("step_slices")
   if (n_slices > w->W) n_slices = w->W;
-  if (n_slices > kMaxSlices) n_slices = kMaxSlices;
+  if (n_slices > kMaxSlices - 1) n_slices = kMaxSlices - 1;
   const size_t rpw = (size_t)w->rays_per_world;
+  // Copies of the previous pipelined tick may still be reading d_ranges / d_idx.  Sliced the same
+  // way, slice s only has to wait for the previous copy of slice s; otherwise (another slice
+  // count, or a tick without outputs, which runs as one launch) everything waits for all of them.
+  const bool same_slicing = w->async_pending && n_slices == w->pending_slices;
+  if (w->async_pending && !same_slicing)
+    for (int s = 0; s < w->pending_slices; ++s) UMRS_CUDA(cudaStreamWaitEvent(w->stream, w->copy_done[s], 0));
   for (int s = 0; s < n_slices; ++s) {
     const int32_t first = (int32_t)((int64_t)w->W * s / n_slices);
     const int32_t end = (int32_t)((int64_t)w->W * (s + 1) / n_slices);
-    if (w->async_pending) UMRS_CUDA(cudaStreamWaitEvent(w->stream, w->copy_done[s], 0));
+    if (same_slicing) UMRS_CUDA(cudaStreamWaitEvent(w->stream, w->copy_done[s], 0));
     int st = world_launch(w, dc, dm, w->stream, first, end - first, s == n_slices - 1);
     if (st != UMRS_OK) return st;
     if (ranges_out == NULL && hit_idx_out == NULL) continue;
@@ -514,11 +543,16 @@ static int step_enqueue(umrs_world* w, const float* cmds, const uint8_t* cmd_mas
   }
   if (pipelined) {
     // the tick is complete when its kernels AND its copies are
-    UMRS_CUDA(cudaEventRecord(w->slice_done[kMaxSlices - 1], w->stream));
-    UMRS_CUDA(cudaStreamWaitEvent(w->copy_stream, w->slice_done[kMaxSlices - 1], 0));
+    UMRS_CUDA(cudaEventRecord(w->kernels_done, w->stream));
+    UMRS_CUDA(cudaStreamWaitEvent(w->copy_stream, w->kernels_done, 0));
     UMRS_CUDA(cudaEventRecord(w->tick_done[w->async_ticks & 3], w->copy_stream));
     w->async_ticks += 1;
-    w->async_pending = ranges_out != NULL || hit_idx_out != NULL;
+    if (ranges_out != NULL || hit_idx_out != NULL) {
+      w->async_pending = true;
+      w->pending_slices = n_slices;
+    }
+    // (a tick without outputs waited for the earlier copies above and starts none: what was
+    // pending stays pending until a wait call)
   }
   return UMRS_OK;
 }
@@ -532,6 +566,88 @@ int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
   UMRS_CUDA(cudaStreamSynchronize(w->stream));
   UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
   w->async_pending = false;
+  if (w->plan.kernel == 1) return capi_read_flags(w->d_flags);   // only the grid walk can raise one
+  return UMRS_OK;
+}
+
+int umrs_world_check(umrs_world* w) {
+  if (w == NULL) return UMRS_ERR_INVALID;
+  UMRS_CUDA(cudaDeviceSynchronize());
+  return capi_read_flags(w->d_flags);
+}
+
+// ---- checkpoint / resume -----------------------------------------------------------------
+namespace {
+struct StateHeader {
+  uint32_t magic, version;
+  int32_t W, R, H, O;
+  uint64_t seed, step;
+  uint64_t bytes;
+};
+constexpr uint32_t kStateMagic = 0x53524D55u;   // "UMRS"
+uint64_t state_bytes(const umrs_world* w) {
+  return sizeof(StateHeader) + sizeof(RobotState) * (uint64_t)w->W * w->R +
+         sizeof(HumanState) * (uint64_t)w->W * w->H + sizeof(float) * 3ull * (uint64_t)w->W * w->O;
+}
+}  // namespace
+
+int umrs_world_state_size(const umrs_world* w, uint64_t* bytes) {
+  if (w == NULL || bytes == NULL) return UMRS_ERR_INVALID;
+  *bytes = state_bytes(w);
+  return UMRS_OK;
+}
+
+int umrs_world_get_state(umrs_world* w, void* blob, uint64_t capacity) {
+  if (w == NULL || blob == NULL || capacity < state_bytes(w)) return UMRS_ERR_INVALID;
+  UMRS_CUDA(cudaDeviceSynchronize());   // the last step may have run on a caller stream
+  StateHeader h;
+  memset(&h, 0, sizeof(h));
+  h.magic = kStateMagic; h.version = 1;
+  h.W = w->W; h.R = w->R; h.H = w->H; h.O = w->O;
+  h.seed = w->desc.seed; h.step = w->step; h.bytes = state_bytes(w);
+  unsigned char* p = static_cast<unsigned char*>(blob);
+  memcpy(p, &h, sizeof(h));
+  p += sizeof(h);
+  const size_t nr = sizeof(RobotState) * (size_t)w->W * w->R, nh = sizeof(HumanState) * (size_t)w->W * w->H;
+  const size_t no = sizeof(float) * 3 * (size_t)w->W * w->O;
+  UMRS_CUDA(cudaMemcpy(p, w->d_rs[w->cur], nr, cudaMemcpyDeviceToHost));
+  p += nr;
+  if (nh) UMRS_CUDA(cudaMemcpy(p, w->d_hs[w->cur], nh, cudaMemcpyDeviceToHost));
+  p += nh;
+  if (no) UMRS_CUDA(cudaMemcpy(p, w->d_static, no, cudaMemcpyDeviceToHost));
+  return UMRS_OK;
+}
+
+int umrs_world_set_state(umrs_world* w, const void* blob, uint64_t bytes) {
+  if (w == NULL || blob == NULL || bytes < sizeof(StateHeader)) return UMRS_ERR_INVALID;
+  StateHeader h;
+  memcpy(&h, blob, sizeof(h));
+  if (h.magic != kStateMagic || h.version != 1 || h.W != w->W || h.R != w->R || h.H != w->H || h.O != w->O ||
+      h.seed != w->desc.seed || h.bytes != state_bytes(w) || bytes < h.bytes) {
+    capi_set_error("umrs_world_set_state: snapshot of another world shape or seed");
+    return UMRS_ERR_INVALID;
+  }
+  UMRS_CUDA(cudaDeviceSynchronize());
+  w->async_pending = false;
+  const unsigned char* p = static_cast<const unsigned char*>(blob) + sizeof(h);
+  const size_t WR = (size_t)w->W * w->R;
+  const size_t nr = sizeof(RobotState) * WR, nh = sizeof(HumanState) * (size_t)w->W * w->H;
+  const size_t no = sizeof(float) * 3 * (size_t)w->W * w->O;
+  UMRS_CUDA(cudaMemcpy(w->d_rs[w->cur], p, nr, cudaMemcpyHostToDevice));
+  // the convenience pose copy follows the state
+  std::vector<float> pose(WR * 3);
+  const RobotState* rs = reinterpret_cast<const RobotState*>(p);
+  for (size_t i = 0; i < WR; ++i) {
+    RobotState one;
+    memcpy(&one, rs + i, sizeof(one));
+    for (int k = 0; k < 3; ++k) pose[3 * i + k] = one.pose[k];
+  }
+  UMRS_CUDA(cudaMemcpy(w->d_pose, pose.data(), sizeof(float) * WR * 3, cudaMemcpyHostToDevice));
+  p += nr;
+  if (nh) UMRS_CUDA(cudaMemcpy(w->d_hs[w->cur], p, nh, cudaMemcpyHostToDevice));
+  p += nh;
+  if (no) UMRS_CUDA(cudaMemcpy(w->d_static, p, no, cudaMemcpyHostToDevice));
+  w->step = h.step;
   return UMRS_OK;
 }
 
