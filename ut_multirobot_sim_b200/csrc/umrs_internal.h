@@ -94,7 +94,7 @@ struct ScanCommon {
   int32_t max_rows;              // source rows a fan can touch (smem sizing)
   int32_t max_rays;              // largest num_rays of any fan of the launch (smem sizing)
   int32_t multipass;             // a fan's source set can exceed cap (keeps best_q in smem)
-  uint32_t smem_off[16];         // byte offsets of the shared-memory arrays (smem_layout), filled by the
+  uint32_t smem_off[17];         // byte offsets of the shared-memory arrays (smem_layout) + total, filled by the
                                  // launch functions so that no thread recomputes the carve-up
 };
 

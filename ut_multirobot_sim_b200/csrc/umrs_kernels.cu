@@ -63,23 +63,56 @@
 namespace umrs {
 
 // ---- shared-memory carve-up --------------------------------------------------
+// Checked build (-DUMRS_CHECKED; compute-sanitizer is closed on this pool): every array of the
+// carve-up carries its allocated length and every index / pointer offset is asserted against it
+// (a device assert prints file:line and fails the launch), as are the raw shared-address loads of
+// the ray loop.  The whole GPU test suite runs against that build (scripts/checked_build.sh).
+// Shipped build: plain pointers, nothing.
+#ifdef UMRS_CHECKED
+#include <assert.h>
+#define UMRS_ASSERT(c) assert(c)
+template <typename T>
+struct Arr {
+  T* p;
+  int n;
+  __device__ __forceinline__ T& operator[](int i) const { assert(i >= 0 && i < n); return p[i]; }
+  __device__ __forceinline__ T* operator+(int i) const { assert(i >= 0 && i <= n); return p + i; }
+  __device__ __forceinline__ operator T*() const { return p; }
+};
+template <typename T>
+__device__ __forceinline__ Arr<T> make_arr(unsigned char* base, const uint32_t* off, int k) {
+  Arr<T> a;
+  a.p = reinterpret_cast<T*>(base + off[k]);
+  a.n = (int)((off[k + 1] - off[k]) / sizeof(T));   // what smem_layout allocated (16-byte granules)
+  return a;
+}
+#else
+#define UMRS_ASSERT(c) do { } while (0)
+template <typename T>
+using Arr = T*;
+template <typename T>
+__device__ __forceinline__ Arr<T> make_arr(unsigned char* base, const uint32_t* off, int k) {
+  return reinterpret_cast<T*>(base + off[k]);
+}
+#endif
+
 struct SmemView {
-  float4* rec;       // [2*cap] slot s = rec[2s], rec[2s+1]:
-                     //   S1: {p0x,p0y,p1x,p1y} translated | {-, hit index, -, -}
-                     //   S2: {a0, a1, nx, ny}             | {c = n . p0', hit index, -, -}
-  uint16_t* pool;    // [3*cap] bucket entries (slots): chunk c owns [c*K, (c+1)*K)
-  uint16_t* wide;    // [cap/2] slots of candidates that met a full bucket: span-checked per chunk
-  uint16_t* surv;    // [cap] slots that survived the coarse occlusion pre-cull (S1b)
-  float* best_r;     // [max_rays] range of the running winner (the reference's exact expression)
-  float* best_q;     // [max_rays] the quotient the winner was selected on (multi-pass plans only)
-  int32_t* best_i;   // [max_rays] its hit index (-1: none)
-  int32_t* cnt;      // [n_chunks_max] (wrapping entries << 16) | plain entries of the bucket
-  uint32_t* zmax2;   // [n_chunks_max] float bits: squared distance beyond which nothing in the chunk can win
-  int32_t* row_v0;   // [max_rows + 1] first virtual index of source row r
-  int32_t* row_s0;   // [max_rows] first source index of row r (object row: 0)
-  int32_t* ctl;      // [16] n_cand, wide overflow, n_wide, next_chunk, n_rows, wedge flag, n_surv, -, wedge[4]
-  float4* obj;       // [n_obj_lines] world object lines (world step only)
-  float* ent;        // [n_ent][8] {x, y, theta, sin, cos (AngleMod theta), sin, cos (theta), -} (world step only)
+  Arr<float4> rec;       // [2*cap] slot s = rec[2s], rec[2s+1]:
+                         //   S1: {p0x,p0y,p1x,p1y} translated | {-, hit index, -, -}
+                         //   S2: {a0, a1, nx, ny}             | {c = n . p0', hit index, -, -}
+  Arr<uint16_t> pool;    // [3*cap] bucket entries (slots): chunk c owns [c*K, (c+1)*K)
+  Arr<uint16_t> wide;    // [cap/2] slots of candidates that met a full bucket: span-checked per chunk
+  Arr<uint16_t> surv;    // [cap] slots that survived the coarse occlusion pre-cull (S1b)
+  Arr<float> best_r;     // [max_rays] range of the running winner (the reference's exact expression)
+  Arr<float> best_q;     // [max_rays] the quotient the winner was selected on (multi-pass plans only)
+  Arr<int32_t> best_i;   // [max_rays] its hit index (-1: none)
+  Arr<int32_t> cnt;      // [n_chunks_max] (wrapping entries << 16) | plain entries of the bucket
+  Arr<uint32_t> zmax2;   // [n_chunks_max] float bits: squared distance beyond which nothing in the chunk can win
+  Arr<int32_t> row_v0;   // [max_rows + 1] first virtual index of source row r
+  Arr<int32_t> row_s0;   // [max_rows] first source index of row r (object row: 0)
+  Arr<int32_t> ctl;      // [16] n_cand, wide overflow, n_wide, next_chunk, n_rows, wedge flag, n_surv, -, wedge[4]
+  Arr<float4> obj;       // [n_obj_lines] world object lines (world step only)
+  Arr<float> ent;        // [n_ent][8] {x, y, theta, sin, cos (AngleMod theta), sin, cos (theta), -} (world step only)
 };
 enum { kCtlNCand = 0, kCtlWideOverflow = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4,
        kCtlWedgeOn = 5, kCtlNSurv = 6, kCtlWedge = 8 /* 4 floats: e1x, e1y, e2x, e2y */ };
@@ -132,27 +165,27 @@ size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int
 // The offsets come with the launch parameters (constant bank): see fill_smem_offsets.
 __device__ __forceinline__ SmemView carve(unsigned char* base, const ScanCommon& c) {
   SmemView v;
-  v.rec = reinterpret_cast<float4*>(base + c.smem_off[0]);
-  v.surv = reinterpret_cast<uint16_t*>(base + c.smem_off[1]);
-  v.pool = reinterpret_cast<uint16_t*>(base + c.smem_off[4]);
-  v.wide = reinterpret_cast<uint16_t*>(base + c.smem_off[5]);
-  v.best_r = reinterpret_cast<float*>(base + c.smem_off[6]);
-  v.best_i = reinterpret_cast<int32_t*>(base + c.smem_off[7]);
-  v.cnt = reinterpret_cast<int32_t*>(base + c.smem_off[8]);
-  v.zmax2 = reinterpret_cast<uint32_t*>(base + c.smem_off[9]);
-  v.row_v0 = reinterpret_cast<int32_t*>(base + c.smem_off[10]);
-  v.row_s0 = reinterpret_cast<int32_t*>(base + c.smem_off[11]);
-  v.ctl = reinterpret_cast<int32_t*>(base + c.smem_off[12]);
-  v.obj = reinterpret_cast<float4*>(base + c.smem_off[13]);
-  v.ent = reinterpret_cast<float*>(base + c.smem_off[14]);
-  v.best_q = reinterpret_cast<float*>(base + c.smem_off[15]);
+  v.rec = make_arr<float4>(base, c.smem_off, 0);
+  v.surv = make_arr<uint16_t>(base, c.smem_off, 1);
+  v.pool = make_arr<uint16_t>(base, c.smem_off, 4);
+  v.wide = make_arr<uint16_t>(base, c.smem_off, 5);
+  v.best_r = make_arr<float>(base, c.smem_off, 6);
+  v.best_i = make_arr<int32_t>(base, c.smem_off, 7);
+  v.cnt = make_arr<int32_t>(base, c.smem_off, 8);
+  v.zmax2 = make_arr<uint32_t>(base, c.smem_off, 9);
+  v.row_v0 = make_arr<int32_t>(base, c.smem_off, 10);
+  v.row_s0 = make_arr<int32_t>(base, c.smem_off, 11);
+  v.ctl = make_arr<int32_t>(base, c.smem_off, 12);
+  v.obj = make_arr<float4>(base, c.smem_off, 13);
+  v.ent = make_arr<float>(base, c.smem_off, 14);
+  v.best_q = make_arr<float>(base, c.smem_off, 15);
   return v;
 }
 
 // Host side of carve(): returns the CTA's dynamic shared-memory size.
 static size_t fill_smem_offsets(ScanCommon& c, int n_obj_lines, int n_ent) {
   const SmemOffsets L = smem_layout(c.cap, c.max_rows, c.max_rays, n_obj_lines, n_ent, c.multipass);
-  for (int k = 0; k < 16; ++k) c.smem_off[k] = (uint32_t)L.o[k];
+  for (int k = 0; k <= 16; ++k) c.smem_off[k] = (uint32_t)L.o[k];
   return L.o[16];
 }
 
@@ -651,6 +684,7 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
 #define UMRS_TEST(S, COVER_EXPR)                                                          \
     {                                                                                     \
       const int s_ = (int)(S);                                                            \
+      UMRS_ASSERT(s_ >= 0 && s_ < n_cand);                                                \
       const unsigned ra_ = rec_addr((unsigned)s_, rec_s);                                 \
       const float4 r4 = lds_f4(ra_);                          /* broadcast LDS.128 */     \
       const float cc = lds_f1_off16(ra_);                                                 \
@@ -668,6 +702,9 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
       const int packed = sm.cnt[chunk];
       n_plain = packed & 0xffff;
       n_wrap = packed >> 16;
+#ifdef UMRS_CHECKED
+      assert(n_plain + n_wrap <= K && (chunk + 1) * K <= sm.pool.n);
+#endif
       unsigned bp = bucket_s;
       int n = n_plain;
       for (; n >= 4; n -= 4, bp += 8) {               // four candidates in flight
@@ -704,6 +741,7 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
       if (counters != nullptr && lane == 0) atomicAdd(counters + 4, 1ull);
       int best_idx = best_s >= 0 ? lds_i1_off20(rec_addr((unsigned)best_s, rec_s)) : prev_i;
       auto careful = [&](int slot) {
+        UMRS_ASSERT(slot >= 0 && slot < n_cand);
         const unsigned ra = rec_addr((unsigned)slot, rec_s);
         const float4 r4 = lds_f4(ra);
         if (!cast_covers(r4.x, r4.y, a)) return;
