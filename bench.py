@@ -89,14 +89,15 @@ def config_dict(args, n_segs):
 
 
 def make_inputs(args, rank, world_size):
+    """The whole job's poses and command sets (every rank builds the same arrays and takes its block)."""
     import ut_multirobot_sim_b200 as umrs
     from ut_multirobot_sim_b200 import synth
     from ut_multirobot_sim_b200.shard import shard_worlds
     W_total = total_worlds(args)
     base, per = shard_worlds(W_total, rank, world_size)
     segs = umrs.map_cleanup(synth.floorplan_segments(args.map_segments, extent=EXTENT, seed=1234))
-    poses = synth.sample_free_poses_fast(segs, W_total, EXTENT, seed=11)[base:base + per]
-    cmds = [synth.ackermann_commands(W_total, 1, s, seed=42)[base:base + per] for s in range(8)]
+    poses = synth.sample_free_poses_fast(segs, W_total, EXTENT, seed=11)
+    cmds = [synth.ackermann_commands(W_total, 1, s, seed=42) for s in range(8)]
     return segs, poses, cmds, per, base
 
 
@@ -300,12 +301,19 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    segs, poses, cmd_sets, W, base = make_inputs(args, rank, world_size)
+    segs, poses_all, cmds_all, W, base = make_inputs(args, rank, world_size)
+    W_total = total_worlds(args)
     vmap = umrs.VectorMap(lines=segs)
     car = umrs.default_robot("ut_automata")
-    world = umrs.World(vmap, [car], W, dt=0.025, seed=42, laser_noise=True, motion_noise=True,
-                       world_index_base=base, write_hit_idx=False)
-    world.SetPose(poses.reshape(W, 1, 3))
+
+    def make_world(b, n):
+        wd = umrs.World(vmap, [car], n, dt=0.025, seed=42, laser_noise=True, motion_noise=True,
+                        world_index_base=b, write_hit_idx=False)
+        wd.SetPose(np.ascontiguousarray(poses_all[b:b + n]).reshape(n, 1, 3))
+        return wd
+
+    world = make_world(base, W)
+    cmd_sets = [np.ascontiguousarray(c[base:base + W]) for c in cmds_all]
     rays_per_step = W * N_RAYS
 
     stream = torch.cuda.Stream()
@@ -333,11 +341,11 @@ def run_b200(args):
         ms = sum(a.elapsed_time(b) for a, b in zip(ev0, ev1))
         return ms, l1 - l0
 
-    def e2e_leg(pipelined):
+    def e2e_leg(world, b, W, pipelined):
         # host buffers (pinned), through the public host-buffer C-ABI calls.  pipelined: successive
         # ticks through umrs_world_step_async into two output buffers in turn, the previous tick's
         # output waited for (and read) while the next one runs; else one synchronous call per tick.
-        h_cmds = [torch.from_numpy(c).pin_memory() for c in cmd_sets]
+        h_cmds = [torch.from_numpy(np.ascontiguousarray(c[b:b + W])).pin_memory() for c in cmds_all]
         h_out = [torch.empty((W, N_RAYS), dtype=torch.float32).pin_memory() for _ in range(2)]
         for s in range(min(Wm, 3)):
             world.step_raw(h_cmds[s % 8].data_ptr(), None, h_out[0].data_ptr(), None)
@@ -365,12 +373,8 @@ def run_b200(args):
     ms_dev, launches = device_leg()
     clocks = sampler.result()
     ms_dev = max_over_ranks(ms_dev)
-    ms_sync, h2d, d2h, _ = e2e_leg(False)
-    ms_sync = max_over_ranks(ms_sync)
-    ms_e2e, h2d, d2h, _ = e2e_leg(True)
-    ms_e2e = max_over_ranks(ms_e2e)
-
-    # plain pinned D2H of one step's output, timed in this run: the PCIe roofline of `e2e`
+    # plain pinned D2H of one step's output, timed in this run on every rank at once: the PCIe
+    # roofline of `e2e`, and (N > 1) the weights of the host-buffer sharding
     def pcie_peak():
         n_bytes = W * N_RAYS * 4
         dev = torch.empty(n_bytes, dtype=torch.uint8, device="cuda")
@@ -387,14 +391,25 @@ def run_b200(args):
         torch.cuda.synchronize()
         return reps * n_bytes / (e0.elapsed_time(e1) * 1e-3) / 1e9
 
-    pcie_gbs = pcie_peak()
-    if world_size > 1:     # the rank with the slowest link sets the step
-        t = torch.tensor([pcie_gbs], dtype=torch.float64, device="cuda")
-        lst = [torch.zeros_like(t) for _ in range(world_size)]
-        dist.all_gather(lst, t)
-        pcie_all = [float(x.item()) for x in lst]
+    pcie_all = shard.exchange_rates(pcie_peak())      # one all-gather, before the timed e2e region
+    # Host-buffer stepping is bound by each GPU's link to host memory, and on this pool's 8-GPU box the
+    # links are not equal (12.6 vs 22 GB/s with all ranks copying): the e2e legs shard the SAME job in
+    # proportion to the measured rates (contiguous blocks, global world indices: same bits), so that
+    # every rank's copy takes the same time.  The device-resident `value` keeps the uniform blocks.
+    if world_size > 1:
+        base_e, W_e = shard.shard_worlds_weighted(W_total, rank, pcie_all)
+        world_e = make_world(base_e, W_e)
     else:
-        pcie_all = [pcie_gbs]
+        base_e, W_e, world_e = base, W, world
+    ms_sync, _, _, _ = e2e_leg(world_e, base_e, W_e, False)
+    ms_sync = max_over_ranks(ms_sync)
+    ms_e2e, _, _, _ = e2e_leg(world_e, base_e, W_e, True)
+    ms_e2e = max_over_ranks(ms_e2e)
+    ms_e2e_uniform = None
+    if world_size > 1:
+        ms_e2e_uniform, _, _, _ = e2e_leg(world, base, W, True)
+        ms_e2e_uniform = max_over_ranks(ms_e2e_uniform)
+    h2d, d2h = W_total * 3 * 4, W_total * N_RAYS * 4      # whole job, per step
 
     # sustained leg: back-to-back steps for >= --sustained-seconds, no flush, clocks sampled
     def sustained_leg():
@@ -476,15 +491,21 @@ def run_b200(args):
                 "candidates instead of its occlusion-trimmed render; the reference's own bits are the opt-in "
                 "reference render (legs.reference_render_*)",
         "env_steps_per_sec": W * world_size * K / (ms_dev * 1e-3),
-        "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": h2d * world_size,
-                "d2h_bytes_per_step": d2h * world_size, "ms_per_step": ms_e2e / K,
+        "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K,
                 "env_steps_per_sec": W * world_size * K / (ms_e2e * 1e-3),
                 "call": "umrs_world_step_async + umrs_world_wait_outputs (ticks pipelined, two pinned output buffers)",
                 "pcie": {"achieved_gbs": (d2h + h2d) / (ms_e2e / K * 1e-3) / 1e9,
-                         "peak_gbs": min(pcie_all), "peak_gbs_per_rank": pcie_all,
-                         "frac": (d2h + h2d) / (ms_e2e / K * 1e-3) / 1e9 / min(pcie_all),
-                         "peak_source": "a plain pinned device->host copy of one step's ranges (%d bytes), 20 back to back, "
-                                        "timed in this run on every rank at once; the slowest rank's link" % d2h},
+                         "peak_gbs": sum(pcie_all), "peak_gbs_per_rank": pcie_all,
+                         "frac": (d2h + h2d) / (ms_e2e / K * 1e-3) / 1e9 / sum(pcie_all),
+                         "peak_source": "sum over ranks of a plain pinned device->host copy of a rank's ranges "
+                                        "(%d bytes, 20 back to back), all ranks copying at once, timed in this run" % (W * N_RAYS * 4)},
+                "sharding": {"policy": "uniform contiguous blocks" if world_size == 1 else
+                             "contiguous blocks in proportion to each rank's measured device->host rate "
+                             "(shard_worlds_weighted; global world indices, same bits as the uniform blocks)",
+                             "worlds_this_rank": W_e,
+                             "uniform_blocks": None if ms_e2e_uniform is None else {
+                                 "value": total_rays * K / (ms_e2e_uniform * 1e-3), "ms_per_step": ms_e2e_uniform / K}},
                 "synchronous": {"value": total_rays * K / (ms_sync * 1e-3), "ms_per_step": ms_sync / K,
                                 "call": "umrs_world_step"}},
         "gpu_launches": int(launches),

@@ -21,6 +21,44 @@ def shard_worlds(total_worlds, rank, world_size):
     return base, count
 
 
+def shard_worlds_weighted(total_worlds, rank, weights):
+    """Contiguous block of rank `rank` when rank r should get a share proportional to weights[r]
+    (e.g. its measured device->host link rate, for host-buffer stepping on a box whose GPUs do
+    not all have the same path to host memory): returns (base, count).  Exact partition of
+    [0, total_worlds): shares are floored and the remainder goes to the largest fractional
+    parts (ties: lowest rank), so every rank computes the same table from the same weights.
+    Worlds keep their global index (`world_index_base`), so the Philox streams -- every noise
+    sample and pose -- are those of the unsharded job whatever the weights."""
+    n = len(weights)
+    if n <= 0 or not (0 <= rank < n) or total_worlds < 0:
+        raise ValueError("bad shard request: total=%r rank=%r weights=%r" % (total_worlds, rank, weights))
+    w = [float(x) if (x == x and x > 0.0) else 0.0 for x in weights]
+    tot = sum(w)
+    if tot <= 0.0:
+        return shard_worlds(total_worlds, rank, n)
+    exact = [total_worlds * x / tot for x in w]
+    counts = [int(e) for e in exact]
+    rest = total_worlds - sum(counts)
+    order = sorted(range(n), key=lambda r: (-(exact[r] - counts[r]), r))
+    for r in order[:rest]:
+        counts[r] += 1
+    return sum(counts[:rank]), counts[rank]
+
+
+def exchange_rates(local_rate, group=None, device=None):
+    """All-gather of one float per rank (a measured link rate) -> list indexed by rank.  Called once,
+    before any timed region; the only other exchange of the design is reduce_stats."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return [float(local_rate)]
+    dev = device if device is not None else ("cuda" if dist.get_backend(group) == "nccl" else "cpu")
+    t = torch.tensor([float(local_rate)], dtype=torch.float64, device=dev)
+    out = [torch.zeros_like(t) for _ in range(dist.get_world_size(group))]
+    dist.all_gather(out, t, group=group)
+    return [float(x.item()) for x in out]
+
+
 def reduce_stats(stats, group=None, device=None):
     """All-reduce of World.stats() dicts {hits, min, max, sum} over the ranks."""
     import torch
