@@ -383,6 +383,10 @@ int umrs_config_human_params(const umrs_config* cfg, umrs_human_params* out, int
  *   "cap"          candidate slots per pass, 32..4064 (0 = default 1536)
  *   "grid_from"    map size from which the uniform-grid walk is picked (0 = default 4096)
  *   "step_slices"  world slices of a host-buffer tick, 1..15 (0 = auto)
+ *   "tma_stage"    -1 auto | 0 | 1: stage the fan's source rows into shared memory with bulk copies
+ *                  (cp.async.bulk + mbarrier) instead of per-thread loads; read when a plan is made
+ *                  (world creation / scan call).  Only variant builds (-DUMRS_TMA_STAGE) contain the
+ *                  code: measured slower on every plan (profiles/r2_tma_ab.txt), no effect otherwise
  * UMRS_ERR_INVALID for an unknown key or a value out of range. */
 int umrs_tuning_set(const char* key, int32_t value);
 int umrs_tuning_get(const char* key, int32_t* value);

@@ -23,6 +23,9 @@ namespace umrs {
 static thread_local std::string g_last_cuda_error;
 static std::atomic<uint64_t> g_launches{0};
 Tuning g_tuning;
+// Bulk-copy staging when the "tma_stage" hook is on auto: off -- it lost the same-box A/B on every
+// plan (profiles/r2_tma_ab.txt), and the shipped build does not even contain it (-DUMRS_TMA_STAGE).
+constexpr int kTmaDefault = 0;
 
 void note_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
@@ -80,7 +83,7 @@ namespace umrs {
 // shared with umrs_world.cu
 int capi_cuda_fail(cudaError_t e, const char* what) { return cuda_fail(e, what); }
 void capi_set_error(const char* msg) { g_last_cuda_error = msg; }
-struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; int32_t multipass; };
+struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; int32_t multipass; int32_t tma_stage; };
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
 void capi_map_segments(const umrs_map* m, const float4** segs_map_order, int32_t* n);
@@ -263,15 +266,23 @@ int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t ma
   // the whole source set of any fan fits one pass <=> no per-ray quotient array
   int mp = need > cap ? 1 : 0;
   // shrink the per-pass slots until the CTA fits the opt-in shared memory
-  while (cap > 32 && scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent, mp) > (size_t)m->smem_optin) {
+  while (cap > 32 && scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent, mp, 0) > (size_t)m->smem_optin) {
     cap = ((cap / 2) + 31) & ~31;
     mp = 1;
   }
   pl.multipass = mp;
-  if (scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent, mp) > (size_t)m->smem_optin) {
+  if (scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent, mp, 0) > (size_t)m->smem_optin) {
     capi_set_error("fan does not fit shared memory (too many rays / object lines per world)");
     return UMRS_ERR_UNSUPPORTED;
   }
+  // Bulk-copy (TMA) staging of the source rows (umrs_kernels.cu: stage_*).  K1: the whole map, one copy,
+  // only where every fan is single-pass; K2: one copy per grid row.  The staging area re-uses arrays that
+  // are dead during the gather, so it costs at most a little padding.  Default: see kTmaDefault.
+  const int want = g_tuning.tma_stage >= 0 ? g_tuning.tma_stage : kTmaDefault;
+  int tma = 0;
+  if (want && tma_stage_built() && m->n > 0) tma = grid ? 2 : (mp == 0 ? 1 : 0);
+  if (tma && scan_smem_bytes(cap, pl.max_rows, max_rays, n_obj_smem, n_ent, mp, tma) > (size_t)m->smem_optin) tma = 0;
+  pl.tma_stage = tma;
   pl.cap = cap;
   *out = pl;
   return UMRS_OK;
@@ -414,6 +425,7 @@ int umrs_tuning_set(const char* key, int32_t value) {
   else if (k == "cap") { if (value != 0 && (value < 32 || value > 4064)) return UMRS_ERR_INVALID; g_tuning.cap = value; }
   else if (k == "grid_from") { if (value < 0) return UMRS_ERR_INVALID; g_tuning.grid_from = value; }
   else if (k == "step_slices") { if (value < 0 || value > 15) return UMRS_ERR_INVALID; g_tuning.step_slices = value; }
+  else if (k == "tma_stage") { if (value < -1 || value > 1) return UMRS_ERR_INVALID; g_tuning.tma_stage = value; }
   else return UMRS_ERR_INVALID;
   return UMRS_OK;
 }
@@ -425,6 +437,7 @@ int umrs_tuning_get(const char* key, int32_t* value) {
   else if (k == "cap") *value = g_tuning.cap;
   else if (k == "grid_from") *value = g_tuning.grid_from;
   else if (k == "step_slices") *value = g_tuning.step_slices;
+  else if (k == "tma_stage") *value = g_tuning.tma_stage;
   else return UMRS_ERR_INVALID;
   return UMRS_OK;
 }
@@ -450,6 +463,7 @@ int umrs_scan_batch_device(umrs_map* m, const float* obj_segs_dev, int32_t n_obj
   p.c.max_rows = pl.max_rows;
   p.c.max_rays = num_rays;
   p.c.multipass = pl.multipass;
+  p.c.tma_stage = pl.tma_stage;
   p.c.ranges = ranges_dev;
   p.c.hit_idx = hit_idx_dev;
   p.c.counters = nullptr;
@@ -546,7 +560,7 @@ int umrs_scan_batch_reference_render_device(umrs_map* m, const float* obj_segs_d
     float* c = nullptr;
     cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&a), sizeof(float4) * n);
     if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&b), sizeof(float4) * n);
-    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&c), sizeof(float) * n);
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&c), sizeof(float) * ((size_t)kRenderFansPerLaunch * kRenderScratchCWords));
     if (e != cudaSuccess) {
       if (a) cudaFree(a);
       if (b) cudaFree(b);

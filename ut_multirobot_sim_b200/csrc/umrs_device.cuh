@@ -242,6 +242,28 @@ __device__ __forceinline__ bool aabb_keep(float4 s, float lx, float ly, float ma
   return true;
 }
 
+// 1 / x to 1 ulp, one MUFU.RCP (no denormal-scaling wrapper around it).
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// atan2 to 2e-5 rad (Abramowitz & Stegun 4.4.49 on the octant-reduced ratio).
+__device__ __forceinline__ float atan2_coarse(float y, float x) {
+  const float ax = fabsf(x), ay = fabsf(y);
+  const float z = fminf(ax, ay) * rcp_approx(fmaxf(ax, ay));
+  const float z2 = z * z;
+  float r = __fmaf_rn(z2, 0.0208351f, -0.0851330f);
+  r = __fmaf_rn(z2, r, 0.1801410f);
+  r = __fmaf_rn(z2, r, -0.3302995f);
+  r = __fmaf_rn(z2, r, 0.9998660f);
+  r *= z;
+  if (ay > ax) r = 1.57079633f - r;
+  if (x < 0.f) r = 3.14159265f - r;
+  return y < 0.f ? -r : r;
+}
+
 // ---- Philox4x32-10 (counter-based; replaces std::default_random_engine,
 // simulator.h:99-100, ackermann_model.h:17-18) ------------------------------
 __device__ __forceinline__ uint4 philox4x32(uint4 c, uint2 k) {

@@ -80,6 +80,7 @@ struct Tuning {
   int cap = 0;
   int grid_from = 0;
   int step_slices = 0;
+  int tma_stage = -1;   // -1 auto (the plan decides), 0 off, 1 on wherever the plan allows it
 };
 extern Tuning g_tuning;
 
@@ -94,6 +95,10 @@ struct ScanCommon {
   int32_t max_rows;              // source rows a fan can touch (smem sizing)
   int32_t max_rays;              // largest num_rays of any fan of the launch (smem sizing)
   int32_t multipass;             // a fan's source set can exceed cap (keeps best_q in smem)
+  int32_t tma_stage;             // 0: the gather reads the source rows with per-thread loads;
+                                 // 1: K1, the whole map is staged into shared memory by ONE bulk copy
+                                 //    (cp.async.bulk + mbarrier) issued before the entity steps;
+                                 // 2: K2, one bulk copy per grid row, issued once the rows are known
   uint32_t smem_off[17];         // byte offsets of the shared-memory arrays (smem_layout) + total, filled by the
                                  // launch functions so that no thread recomputes the carve-up
 };
@@ -153,7 +158,7 @@ struct RenderScanParams {
   float* ranges;           // [n_fans][num_rays]
   float4* scratch_lines;   // [fans per launch][2000] candidate list, then the cast constants
   float4* scratch_scene;   // [fans per launch][2000]
-  float* scratch_c;        // [fans per launch][2000]
+  float* scratch_c;        // [fans per launch][kRenderScratchCWords]: cast constants, intervals, candidate list
   int32_t fan_begin;       // first fan of this launch (scratch slot = fan - fan_begin)
   // world mode (world_R > 0): fan g = (world g / R, robot g % R) of a world step; fans = the
   // step's fan_params, object lines per world minus the robot's own body, per-robot laser
@@ -170,13 +175,15 @@ struct RenderScanParams {
   uint32_t key0, key1, step_lo, step_hi;
   int32_t world_base;
 };
+constexpr int kRenderScratchCWords = 2000 + 2 * 2000 + 1000;   // per fan: float c[2000], uint2 iv[2000], u16 list[2000]
 constexpr int kRenderFansPerLaunch = 4096;   // 295 MB of scratch; ~1.15 resident waves of warps on 148 SMs
 cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, int fan_end,
                                     cudaStream_t stream);
 
 // Dynamic shared memory of one fan CTA.
 size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent,
-                       int multipass);
+                       int multipass, int tma_stage);
+bool tma_stage_built();   // the bulk-copy staging variant is compiled in (-DUMRS_TMA_STAGE)
 
 cudaError_t launch_scan_batch(const ScanBatchParams& p, cudaStream_t stream);
 cudaError_t launch_world_step(const WorldStepParams& p, cudaStream_t stream);

@@ -62,6 +62,13 @@
 
 namespace umrs {
 
+// Bulk-copy (TMA) staging of the source rows: variant builds only, see stage_* below.
+#ifdef UMRS_TMA_STAGE
+constexpr bool kTmaBuilt = true;
+#else
+constexpr bool kTmaBuilt = false;
+#endif
+
 // ---- shared-memory carve-up --------------------------------------------------
 // Checked build (-DUMRS_CHECKED; compute-sanitizer is closed on this pool): every array of the
 // carve-up carries its allocated length and every index / pointer offset is asserted against it
@@ -111,11 +118,13 @@ struct SmemView {
   Arr<int32_t> row_v0;   // [max_rows + 1] first virtual index of source row r
   Arr<int32_t> row_s0;   // [max_rows] first source index of row r (object row: 0)
   Arr<int32_t> ctl;      // [16] n_cand, wide overflow, n_wide, next_chunk, n_rows, wedge flag, n_surv, -, wedge[4]
+  float4* stage;         // tma_stage: [cap] raw source segments, over pad + pool + wide + best_r + best_i
   Arr<float4> obj;       // [n_obj_lines] world object lines (world step only)
   Arr<float> ent;        // [n_ent][8] {x, y, theta, sin, cos (AngleMod theta), sin, cos (theta), -} (world step only)
 };
 enum { kCtlNCand = 0, kCtlWideOverflow = 1, kCtlNWide = 2, kCtlNextChunk = 3, kCtlNRows = 4,
-       kCtlWedgeOn = 5, kCtlNSurv = 6, kCtlWedge = 8 /* 4 floats: e1x, e1y, e2x, e2y */ };
+       kCtlWedgeOn = 5, kCtlNSurv = 6, kCtlWedge = 8 /* 4 floats: e1x, e1y, e2x, e2y */,
+       kCtlBar = 12 /* 8 bytes: the staging mbarrier (tma_stage) */ };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
@@ -127,14 +136,25 @@ __host__ __device__ inline size_t pool_entries(int cap, int n_chunks_max) {
 
 struct SmemOffsets { size_t o[17]; };
 
+// Staging area of the bulk-copy variant (tma_stage): the raw source rows, 16 B per segment, land
+// in the arrays that are dead until the bucket fill / ray loop -- pool, wide, best_r, best_i, which
+// are contiguous -- preceded by whatever padding makes the area hold `cap` segments.
+__host__ __device__ inline size_t stage_pad(int cap, int max_rays, int n_chunks, int tma_stage) {
+  if (!tma_stage) return 0;
+  const size_t have = align16(sizeof(uint16_t) * pool_entries(cap, n_chunks)) + align16(sizeof(uint16_t) * (size_t)(cap / 2)) +
+                      align16(sizeof(float) * (size_t)max_rays) + align16(sizeof(int32_t) * (size_t)max_rays);
+  const size_t need = sizeof(float4) * (size_t)cap;
+  return need > have ? need - have : 0;
+}
+
 __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int max_rays,
-                                                   int n_obj_lines, int n_ent, int multipass) {
+                                                   int n_obj_lines, int n_ent, int multipass, int tma_stage) {
   const size_t n_chunks = (size_t)((max_rays + 31) >> 5);
   const size_t sizes[16] = {
       sizeof(float4) * 2 * (size_t)cap,        // rec
       sizeof(uint16_t) * (size_t)cap,          // surv
       0,                                       // (spare)
-      0,                                       // (spare)
+      stage_pad(cap, max_rays, (int)n_chunks, tma_stage),   // stage = this pad + pool + wide + best_r + best_i
       sizeof(uint16_t) * pool_entries(cap, (int)n_chunks),  // pool
       sizeof(uint16_t) * (size_t)(cap / 2),    // wide
       sizeof(float) * (size_t)max_rays,        // best_r
@@ -157,9 +177,11 @@ __host__ __device__ inline SmemOffsets smem_layout(int cap, int max_rows, int ma
   return L;
 }
 
+bool tma_stage_built() { return kTmaBuilt; }
+
 size_t scan_smem_bytes(int cap, int max_rows, int max_rays, int n_obj_lines, int n_ent,
-                       int multipass) {
-  return smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent, multipass).o[16];
+                       int multipass, int tma_stage) {
+  return smem_layout(cap, max_rows, max_rays, n_obj_lines, n_ent, multipass, tma_stage).o[16];
 }
 
 // The offsets come with the launch parameters (constant bank): see fill_smem_offsets.
@@ -179,12 +201,13 @@ __device__ __forceinline__ SmemView carve(unsigned char* base, const ScanCommon&
   v.obj = make_arr<float4>(base, c.smem_off, 13);
   v.ent = make_arr<float>(base, c.smem_off, 14);
   v.best_q = make_arr<float>(base, c.smem_off, 15);
+  v.stage = reinterpret_cast<float4*>(base + c.smem_off[3]);
   return v;
 }
 
 // Host side of carve(): returns the CTA's dynamic shared-memory size.
 static size_t fill_smem_offsets(ScanCommon& c, int n_obj_lines, int n_ent) {
-  const SmemOffsets L = smem_layout(c.cap, c.max_rows, c.max_rays, n_obj_lines, n_ent, c.multipass);
+  const SmemOffsets L = smem_layout(c.cap, c.max_rows, c.max_rays, n_obj_lines, n_ent, c.multipass, c.tma_stage);
   for (int k = 0; k <= 16; ++k) c.smem_off[k] = (uint32_t)L.o[k];
   return L.o[16];
 }
@@ -202,6 +225,59 @@ struct PostProcess {
   float stddev;
   uint32_t key0, key1, step_lo, step_hi, fan_global;
 };
+
+// ---- bulk-copy staging (TMA engine: cp.async.bulk + mbarrier) ---------------------------
+// VARIANT BUILD ONLY (-DUMRS_TMA_STAGE): measured on B200 and rejected for every plan
+// (profiles/r2_tma_ab.txt: -1 % on K1 maps, -25 % on the grid walk; the gather is not
+// latency-bound, and bulk copies bypass the L1 the co-resident fans share).  In the shipped
+// build kTmaBuilt is false and every use below folds away.
+
+// One thread arms the mbarrier with the byte count and issues the copies; the copy engine
+// streams global -> shared memory on its own and completes the barrier's transaction count;
+// every thread then waits on the barrier's phase.  SASS: UBLKCP.S.G, SYNCS.ARRIVE.TRANS64,
+// SYNCS.PHASECHK.TRANS64.TRYWAIT.
+__device__ __forceinline__ void stage_bar_init(int32_t* bar_words) {
+  const unsigned bar = (unsigned)__cvta_generic_to_shared(bar_words);
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+// Arms the barrier for `bytes` in total (one arrival: the issuing thread's).
+__device__ __forceinline__ void stage_expect(int32_t* bar_words, unsigned bytes) {
+  const unsigned bar = (unsigned)__cvta_generic_to_shared(bar_words);
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// bytes: a multiple of 16; src and dst 16-byte aligned.
+__device__ __forceinline__ void stage_copy(void* dst_smem, const void* src_gmem, unsigned bytes, int32_t* bar_words) {
+  const unsigned bar = (unsigned)__cvta_generic_to_shared(bar_words);
+  const unsigned dst = (unsigned)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void stage_wait(int32_t* bar_words, unsigned parity) {
+  const unsigned bar = (unsigned)__cvta_generic_to_shared(bar_words);
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+// The staging area was last written through the generic proxy (buckets / winners of the previous
+// fan): order those writes before the async proxy's.
+__device__ __forceinline__ void stage_fence_generic_to_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// K1: the whole map in ONE bulk copy; issued by one thread as early as possible (it does not
+// depend on the pose, so it runs under the entity steps).
+__device__ __forceinline__ void stage_issue_map(const SmemView& sm, const MapSource& src) {
+  const unsigned bytes = (unsigned)src.n * 16u;
+  stage_expect(sm.ctl + kCtlBar, bytes);
+  if (bytes) stage_copy(sm.stage, src.segs, bytes, sm.ctl + kCtlBar);
+}
 
 // ---- source rows of a fan -----------------------------------------------------------
 // Virtual index space = concatenation of the rows; row r covers virtual
@@ -261,7 +337,8 @@ constexpr float kWedgeMargin = 1e-3f;   // rad; dominates every rounding in the 
 // Virtual indices [v_begin, v_end) of this pass.  Object lines [skip_lo, skip_hi)
 // are the fan's own body.
 __device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
-                       const float4* obj_segs, int skip_lo, int skip_hi, int v_begin, int v_end) {
+                       const float4* obj_segs, int skip_lo, int skip_hi, int v_begin, int v_end,
+                       bool staged) {
   const int n_rows = sm.ctl[kCtlNRows];
   const int lane = threadIdx.x & 31;
   // Back-wedge cull (fans wider than half a turn): the directions no ray of the fan
@@ -291,7 +368,7 @@ __device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
         keep = !(k >= skip_lo && k < skip_hi);
       } else {
         const int si = sm.row_s0[lo] + k;
-        s = __ldg(src.segs + si);
+        s = staged ? sm.stage[v] : __ldg(src.segs + si);   // K1: v == si; K2: rows are staged back to back
         hit = src.orig ? __ldg(src.orig + si) : si;
         keep = true;
       }
@@ -399,13 +476,6 @@ __device__ __forceinline__ void lower_zmax(const SmemView& sm, int li, int hi, i
   for (int c = ca; c <= cb; ++c) atomicMin(&sm.zmax2[c], bits);
 }
 
-// 1 / x to 1 ulp, one MUFU.RCP (no denormal-scaling wrapper around it).
-__device__ __forceinline__ float rcp_approx(float x) {
-  float r;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-  return r;
-}
-
 // ---- S1b: coarse occlusion pre-cull ------------------------------------------------------
 // Most gathered candidates are walls behind nearer walls.  Before the expensive S2
 // work (exact end-point angles, normals, buckets) a cheap pass drops those that
@@ -437,21 +507,6 @@ constexpr float kPreSlack = 1e-3f;
 #define UMRS_PRECULL_MIN 256
 #endif
 constexpr int kPreMinCand = UMRS_PRECULL_MIN;   // fewer candidates than the widest CTA has threads: S2 is one trip anyway
-
-// atan2 to 2e-5 rad (Abramowitz & Stegun 4.4.49 on the octant-reduced ratio).
-__device__ __forceinline__ float atan2_coarse(float y, float x) {
-  const float ax = fabsf(x), ay = fabsf(y);
-  const float z = fminf(ax, ay) * rcp_approx(fmaxf(ax, ay));
-  const float z2 = z * z;
-  float r = __fmaf_rn(z2, 0.0208351f, -0.0851330f);
-  r = __fmaf_rn(z2, r, 0.1801410f);
-  r = __fmaf_rn(z2, r, -0.3302995f);
-  r = __fmaf_rn(z2, r, 0.9998660f);
-  r *= z;
-  if (ay > ax) r = 1.57079633f - r;
-  if (x < 0.f) r = 3.14159265f - r;
-  return y < 0.f ? -r : r;
-}
 
 __device__ void precull_mark(const SmemView& sm, const Lattice& L) {
   const int n_cand = sm.ctl[kCtlNCand];
@@ -819,7 +874,7 @@ __device__ void finalise(const SmemView& sm, const Fan& fan, float* __restrict__
 // ---- one fan, all passes --------------------------------------------------------------
 __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan,
                          const float4* obj_segs, int n_obj, int skip_lo, int skip_hi,
-                         float* ranges, int32_t* hit_idx, const PostProcess& post) {
+                         float* ranges, int32_t* hit_idx, const PostProcess& post, unsigned stage_parity) {
   UMRS_STAMP_INIT;
   const Lattice L = make_lattice(fan.amin, fan.amax, fan.num_rays);
   const int n_chunks = (fan.num_rays + 31) >> 5;
@@ -850,10 +905,26 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
   __syncthreads();
   UMRS_STAMP(c.counters, 1);
   const int v_total = sm.row_v0[sm.ctl[kCtlNRows]];
+  // Bulk-copy staging: single-pass fans only (the area aliases the per-ray winners, which a
+  // multi-pass fan carries from pass to pass).
+  const bool staged = kTmaBuilt && c.tma_stage != 0 && v_total <= c.cap;
+  if (kTmaBuilt && c.tma_stage == 2) {
+    // K2: the rows are known now -- one bulk copy per grid row, back to back in virtual order
+    if (threadIdx.x == 0) {
+      const int n_rows = sm.ctl[kCtlNRows];
+      const int n_src = staged ? sm.row_v0[n_rows - 1] : 0;   // all rows but the object row
+      stage_expect(sm.ctl + kCtlBar, (unsigned)n_src * 16u);
+      for (int r = 0; staged && r < n_rows - 1; ++r) {
+        const int len = sm.row_v0[r + 1] - sm.row_v0[r];
+        if (len > 0) stage_copy(sm.stage + sm.row_v0[r], c.src.segs + sm.row_s0[r], (unsigned)len * 16u, sm.ctl + kCtlBar);
+      }
+    }
+  }
+  if (kTmaBuilt && c.tma_stage != 0) stage_wait(sm.ctl + kCtlBar, stage_parity);   // also when not used: keeps the phases in step
   int pass = 0;
   for (int v0 = 0; v0 < v_total || pass == 0; v0 += c.cap, ++pass) {
     const int v1 = v0 + c.cap < v_total ? v0 + c.cap : v_total;
-    gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1);
+    gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1, staged);
     __syncthreads();
     UMRS_STAMP(c.counters, 2);
     if (pass == 0 || sm.ctl[kCtlNCand] > 0) {   // block-uniform: a later pass may be empty
@@ -912,7 +983,16 @@ __global__ void __launch_bounds__(kThreads, kCtas)
 k_scan_batch(const __grid_constant__ ScanBatchParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const SmemView sm = carve(smem_raw, p.c);
-  for (int f = blockIdx.x; f < p.n_fans; f += gridDim.x) {
+  if (kTmaBuilt && p.c.tma_stage != 0 && threadIdx.x == 0) stage_bar_init(sm.ctl + kCtlBar);
+  unsigned stage_parity = 0;
+  for (int f = blockIdx.x; f < p.n_fans; f += gridDim.x, stage_parity ^= 1u) {
+    if (kTmaBuilt && p.c.tma_stage != 0) {
+      __syncthreads();   // the previous fan is done with the arrays the staging area covers (and the barrier is initialised)
+      if (threadIdx.x == 0) {
+        stage_fence_generic_to_async();
+        if (p.c.tma_stage == 1) stage_issue_map(sm, p.c.src);
+      }
+    }
     const float4 fp = __ldg(p.fans + f);
     Fan fan;
     fan.lx = fp.x; fan.ly = fp.y; fan.amin = fp.z; fan.amax = fp.w;
@@ -924,7 +1004,7 @@ k_scan_batch(const __grid_constant__ ScanBatchParams p) {
     const size_t off = (size_t)f * (size_t)p.num_rays;
     __syncthreads();  // previous fan's finalise is done with the best arrays
     scan_fan(sm, p.c, fan, p.obj_segs, p.n_obj, 0, 0, p.c.ranges + off,
-             p.c.hit_idx ? p.c.hit_idx + off : nullptr, post);
+             p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, stage_parity);
   }
 }
 
@@ -1109,6 +1189,11 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   const double dt = (double)p.dt;  // `const double& dt` bound to float CONFIG_DT
   const int t = threadIdx.x;
   UMRS_STAMP_INIT;
+  if (kTmaBuilt && p.c.tma_stage != 0 && t == 32 % blockDim.x) {
+    // the map streams into shared memory (copy engine) while thread 0 steps the robot
+    stage_bar_init(sm.ctl + kCtlBar);
+    if (p.c.tma_stage == 1) stage_issue_map(sm, p.c.src);
+  }
 
   // ---- phase A: entity steps -> sm.ent[e] = {x, y, theta, sin, cos} ----------
   for (int e = t; e < n_ent; e += blockDim.x) {
@@ -1209,7 +1294,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   const size_t off = (size_t)w * (size_t)p.rays_per_world + (size_t)p.ray_off[r];
   UMRS_STAMP(p.c.counters, 0);
   scan_fan(sm, p.c, fan, sm.obj, p.L_obj, skip_lo, skip_hi, p.c.ranges + off,
-           p.c.hit_idx ? p.c.hit_idx + off : nullptr, post);
+           p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, 0u);
 }
 
 // ---- K3: statistics of a ranges buffer -------------------------------------------

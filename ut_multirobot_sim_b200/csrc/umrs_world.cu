@@ -20,7 +20,7 @@ struct umrs_map;
 namespace umrs {
 int capi_cuda_fail(cudaError_t e, const char* what);
 void capi_set_error(const char* msg);
-struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; int32_t multipass; };
+struct ScanPlan { MapSource src; int32_t cap; int32_t max_rows; int smem_optin; int32_t kernel; int32_t multipass; int32_t tma_stage; };
 int capi_scan_plan(const umrs_map* m, float range_max, int32_t n_obj, int32_t max_rays,
                    int32_t n_obj_smem, int32_t n_ent, ScanPlan* out);
 void capi_map_segments(const umrs_map* m, const float4** segs_map_order, int32_t* n);
@@ -240,7 +240,7 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (ok() && d->write_hit_idx && !d->reference_render) e = dalloc(&w->d_idx, n_rays);
   if (ok() && d->reference_render) e = dalloc(&w->d_render_lines, (size_t)kRenderFansPerLaunch * 2000);
   if (ok() && d->reference_render) e = dalloc(&w->d_render_scene, (size_t)kRenderFansPerLaunch * 2000);
-  if (ok() && d->reference_render) e = dalloc(&w->d_render_c, (size_t)kRenderFansPerLaunch * 2000);
+  if (ok() && d->reference_render) e = dalloc(&w->d_render_c, (size_t)kRenderFansPerLaunch * kRenderScratchCWords);
   if (ok()) e = dalloc(&w->d_fan_params, WR);
   if (ok()) e = dalloc(&w->d_obj_lines, (size_t)w->W * w->L_obj);
   if (ok()) e = dalloc(&w->d_pose, WR * 3);
@@ -399,6 +399,7 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   p.c.max_rows = w->plan.max_rows;
   p.c.max_rays = w->max_rays;
   p.c.multipass = w->plan.multipass;
+  p.c.tma_stage = w->plan.tma_stage;
   p.c.ranges = w->d_ranges;
   p.c.hit_idx = w->d_idx;
   p.c.counters = w->counters_on ? w->d_counters : nullptr;
