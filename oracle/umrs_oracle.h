@@ -8,10 +8,12 @@
  * Parity status: the scan part is PINNED against the reference itself run in
  * the build container (oracle/_ref/libumrs_ref.so = the unmodified
  * vector_map.cpp; fixtures in tests/golden/ made by tests/golden/make_golden.py).
- * The kinematic steps (ackermann/diff-drive/omni/human) are "parity unpinned":
- * their sources need ROS headers and cannot be compiled here, and the
- * reference has no tests or golden vectors for them; they are restated line
- * by line below.
+ * The kinematic steps (ackermann/diff-drive/omni/human) are PINNED as well: the
+ * reference's own model sources compile unmodified into oracle/_ref against
+ * data-only ROS stand-ins (oracle/shim, oracle/ref_models_bridge.cpp), and
+ * tests/test_ref_models.py steps them side by side with the restatement below,
+ * bit for bit after every step.  Tier B is additionally pinned as the exact
+ * nearest hit by an independent float64 ray cast (tests/parity_tools.py).
  */
 #ifndef UMRS_ORACLE_H_
 #define UMRS_ORACLE_H_
