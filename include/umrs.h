@@ -275,7 +275,8 @@ int umrs_world_get_object_lines(umrs_world* world, float* segs_xyxy);
 int umrs_world_step(umrs_world* world, const float* cmds, const uint8_t* cmd_mask,
                     float* ranges_out, int32_t* hit_idx_out);
 /* The same tick, enqueued and not waited for: successive calls pipeline -- the device->host
- * copy of tick k runs while tick k+1 computes -- so a host shell can publish scan k while
+ * copy of tick k runs while tick k+1 computes (the library alternates between two device
+ * output buffers, one launch + one copy per tick) -- so a host shell can publish scan k while
  * the GPU works on k+1.  The caller's buffers belong to the library until waited for: use
  * (at least) two output buffers in turn; pinned memory keeps the copies asynchronous.
  * umrs_world_wait_outputs(w, back): blocks until the outputs of the tick issued `back`

@@ -53,12 +53,16 @@ struct umrs_world {
   cudaEvent_t slice_done[kMaxSlices] = {};
   // pipelined host-buffer ticks (umrs_world_step_async): copy of slice s of the previous tick,
   // and whole-tick completion, both recorded on the copy stream
-  cudaEvent_t copy_done[kMaxSlices] = {};
   cudaEvent_t tick_done[4] = {};
-  cudaEvent_t kernels_done = nullptr;   // all slice kernels of a pipelined tick
+  cudaEvent_t kernels_done = nullptr;   // the kernel(s) of a pipelined tick
+  // Pipelined ticks alternate between TWO device output buffers, so that tick k+1's kernel never
+  // waits for tick k's device->host copy: one launch + one copy per tick (no slices, a handful of
+  // API calls), the copy engine busy back to back.  buf_free[b]: the last copy out of buffer b.
+  cudaEvent_t buf_free[2] = {};
+  bool buf_busy[2] = {false, false};    // a copy out of buffer b may still be in flight
   uint64_t async_ticks = 0;
-  bool async_pending = false;     // device->host copies of a pipelined tick may still be running ...
-  int pending_slices = 0;         // ... in this many slices (copy_done[0 .. pending_slices))
+  bool async_pending = false;     // device->host copies of a pipelined tick may still be running
+  int out_buf = 0;                // the buffer the last step wrote (umrs_world_device_buffers, stats)
   uint64_t step = 0;
   int cur = 0;  // index of the "in" state buffer
   // device
@@ -74,8 +78,10 @@ struct umrs_world {
   float* d_static = nullptr;
   float* d_cmds = nullptr;
   uint8_t* d_mask = nullptr;
-  float* d_ranges = nullptr;
+  float* d_ranges = nullptr;      // output buffer 0 (every synchronous / device-resident step)
   int32_t* d_idx = nullptr;
+  float* d_ranges2 = nullptr;     // output buffer 1 (allocated by the first pipelined tick)
+  int32_t* d_idx2 = nullptr;
   float4* d_fan_params = nullptr;
   float4* d_obj_lines = nullptr;
   float* d_pose = nullptr;
@@ -106,7 +112,7 @@ int umrs_world_destroy(umrs_world* w) {
   if (w->kernels_done) cudaEventDestroy(w->kernels_done);
   void* ptrs[] = {w->d_robots, w->d_humans, w->d_tmpl, w->d_line_ent, w->d_ent_off,
                   w->d_ray_off, w->d_num_rays, w->d_rs[0], w->d_rs[1], w->d_hs[0],
-                  w->d_hs[1], w->d_static, w->d_cmds, w->d_mask, w->d_ranges, w->d_idx,
+                  w->d_hs[1], w->d_static, w->d_cmds, w->d_mask, w->d_ranges, w->d_idx, w->d_ranges2, w->d_idx2,
                   w->d_fan_params, w->d_obj_lines, w->d_pose, w->d_counters, w->d_stats,
                   w->d_render_lines, w->d_render_scene, w->d_render_c};
   for (void* p : ptrs)
@@ -115,7 +121,7 @@ int umrs_world_destroy(umrs_world* w) {
   if (w->copy_stream) cudaStreamDestroy(w->copy_stream);
   for (cudaEvent_t e : w->slice_done)
     if (e) cudaEventDestroy(e);
-  for (cudaEvent_t e : w->copy_done)
+  for (cudaEvent_t e : w->buf_free)
     if (e) cudaEventDestroy(e);
   for (cudaEvent_t e : w->tick_done)
     if (e) cudaEventDestroy(e);
@@ -218,8 +224,8 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (ok()) e = cudaStreamCreateWithFlags(&w->copy_stream, cudaStreamNonBlocking);
   for (int k = 0; k < kMaxSlices; ++k)
     if (ok()) e = cudaEventCreateWithFlags(&w->slice_done[k], cudaEventDisableTiming);
-  for (int k = 0; k < kMaxSlices; ++k)
-    if (ok()) e = cudaEventCreateWithFlags(&w->copy_done[k], cudaEventDisableTiming);
+  for (int k = 0; k < 2; ++k)
+    if (ok()) e = cudaEventCreateWithFlags(&w->buf_free[k], cudaEventDisableTiming);
   for (int k = 0; k < 4; ++k)
     if (ok()) e = cudaEventCreateWithFlags(&w->tick_done[k], cudaEventDisableTiming);
   if (ok()) e = dalloc(&w->d_robots, (size_t)w->R);
@@ -391,7 +397,7 @@ int umrs_world_get_object_lines(umrs_world* w, float* segs) {
 // Launches worlds [first, first + count) of the current tick; `last` closes the tick
 // (state buffers flip, step counter advances).
 static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mask_dev,
-                        cudaStream_t stream, int32_t first, int32_t count, bool last) {
+                        cudaStream_t stream, int32_t first, int32_t count, bool last, int buf = 0) {
   WorldStepParams p;
   memset(&p, 0, sizeof(p));
   p.c.src = w->plan.src;
@@ -400,8 +406,8 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   p.c.max_rays = w->max_rays;
   p.c.multipass = w->plan.multipass;
   p.c.tma_stage = w->plan.tma_stage;
-  p.c.ranges = w->d_ranges;
-  p.c.hit_idx = w->d_idx;
+  p.c.ranges = buf ? w->d_ranges2 : w->d_ranges;
+  p.c.hit_idx = buf ? w->d_idx2 : w->d_idx;
   p.c.counters = w->counters_on ? w->d_counters : nullptr;
   p.c.flags = w->d_flags;
   p.W = w->W; p.R = w->R; p.H = w->H; p.O = w->O;
@@ -445,7 +451,7 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
     q.segs = w->map_segs_in_map_order;
     q.n_map = w->n_map;
     q.fans = w->d_fan_params;
-    q.ranges = w->d_ranges;
+    q.ranges = buf ? w->d_ranges2 : w->d_ranges;
     q.scratch_lines = w->d_render_lines;
     q.scratch_scene = w->d_render_scene;
     q.scratch_c = w->d_render_c;
@@ -468,6 +474,7 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   if (last) {
     w->cur ^= 1;
     w->step += 1;
+    w->out_buf = buf;
   }
   return UMRS_OK;
 }
@@ -478,57 +485,89 @@ int umrs_world_step_device(umrs_world* w, const float* cmds_dev, const uint8_t* 
                            void* stream) {
   if (w == NULL) return UMRS_ERR_INVALID;
   cudaStream_t st = stream ? (cudaStream_t)stream : w->stream;
-  // this launch overwrites d_ranges / d_idx: every device->host copy a pipelined host-buffer tick
-  // still has in flight must be done first (the events stay recorded; the flag is cleared by a wait)
-  if (w->async_pending)
-    for (int s = 0; s < w->pending_slices; ++s) UMRS_CUDA(cudaStreamWaitEvent(st, w->copy_done[s], 0));
-  return world_launch(w, cmds_dev, mask_dev, st, 0, w->W, true);
+  // this launch overwrites output buffer 0: a device->host copy a pipelined host-buffer tick still
+  // has in flight out of it must be done first (the event stays recorded; a wait clears the flag)
+  if (w->buf_busy[0]) UMRS_CUDA(cudaStreamWaitEvent(st, w->buf_free[0], 0));
+  return world_launch(w, cmds_dev, mask_dev, st, 0, w->W, true, 0);
 }
 
 }  // extern "C"
 
+// The two device output buffers of the pipelined path exist from the first pipelined tick on.
+static int ensure_second_buffers(umrs_world* w) {
+  const size_t n_rays = (size_t)w->W * w->rays_per_world;
+  if (w->d_ranges2 == nullptr) {
+    UMRS_CUDA(dalloc(&w->d_ranges2, n_rays));
+    UMRS_CUDA(cudaMemsetAsync(w->d_ranges2, 0, sizeof(float) * n_rays, w->stream));
+  }
+  if (w->d_idx != nullptr && w->d_idx2 == nullptr) UMRS_CUDA(dalloc(&w->d_idx2, n_rays));
+  return UMRS_OK;
+}
+
 // One tick with host buffers, enqueued on the world's two streams (no synchronisation here).
-// pipelined: this tick may follow one whose device->host copies are still running -- a slice's
-// kernel then waits for the previous tick's copy of the same slice (it overwrites that part
-// of d_ranges), and the tick's completion is recorded for umrs_world_wait_outputs.
+//   blocking tick (umrs_world_step): cut into world slices on output buffer 0 -- the device->host
+//     copy of slice k runs on the copy stream while slice k+1 computes, so the call costs about
+//     max(kernel, PCIe) + one slice instead of their sum;
+//   pipelined tick (umrs_world_step_async): ONE launch into the output buffer that is not being
+//     copied, ONE copy behind it; tick k's copy runs under tick k+1's kernel, and the kernel only
+//     ever waits for the copy of tick k-1 (long done in steady state).  Seven API calls per tick.
 static int step_enqueue(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
                         float* ranges_out, int32_t* hit_idx_out, bool pipelined) {
   if (w == NULL) return UMRS_ERR_INVALID;
   if (hit_idx_out != NULL && w->d_idx == NULL) return UMRS_ERR_INVALID;   // also: reference-render worlds
   const size_t WR = (size_t)w->W * w->R;
+  const size_t n_rays = (size_t)w->W * w->rays_per_world;
+  if (!pipelined && w->async_pending) {
+    // a blocking tick after pipelined ones: let their copies finish first
+    UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
+    w->async_pending = false;
+    w->buf_busy[0] = w->buf_busy[1] = false;
+  }
+  int buf = 0;
+  if (pipelined) {
+    const int st2 = ensure_second_buffers(w);
+    if (st2 != UMRS_OK) return st2;
+    buf = (int)(w->async_ticks & 1);
+    if (w->buf_busy[buf]) UMRS_CUDA(cudaStreamWaitEvent(w->stream, w->buf_free[buf], 0));
+  }
   if (cmds)
     UMRS_CUDA(cudaMemcpyAsync(w->d_cmds, cmds, sizeof(float) * WR * 3, cudaMemcpyHostToDevice, w->stream));
   if (cmds && cmd_mask)
     UMRS_CUDA(cudaMemcpyAsync(w->d_mask, cmd_mask, WR, cudaMemcpyHostToDevice, w->stream));
-  // The tick is cut into world slices: the device->host copy of slice k runs on the
-  // copy stream while slice k+1 computes, so the call costs ~max(kernel, PCIe)
-  // instead of their sum.  Worlds are independent, so slicing changes nothing else.
   const float* dc = cmds ? w->d_cmds : nullptr;
   const uint8_t* dm = (cmds && cmd_mask) ? w->d_mask : nullptr;
-  // synchronous tick: 8 slices (first-slice latency matters); pipelined ticks: 4 (in steady state
-  // the copy engine never idles and fewer, larger copies run faster) -- measured on B200
-  if (!pipelined && w->async_pending) {
-    // a blocking tick after pipelined ones slices differently: let their copies finish first
-    UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
-    w->async_pending = false;
+  if (pipelined) {
+    const int st = world_launch(w, dc, dm, w->stream, 0, w->W, true, buf);
+    if (st != UMRS_OK) return st;
+    // the tick is complete when its kernel AND its copies are
+    UMRS_CUDA(cudaEventRecord(w->kernels_done, w->stream));
+    UMRS_CUDA(cudaStreamWaitEvent(w->copy_stream, w->kernels_done, 0));
+    if (ranges_out)
+      UMRS_CUDA(cudaMemcpyAsync(ranges_out, buf ? w->d_ranges2 : w->d_ranges, sizeof(float) * n_rays,
+                                cudaMemcpyDeviceToHost, w->copy_stream));
+    if (hit_idx_out)
+      UMRS_CUDA(cudaMemcpyAsync(hit_idx_out, buf ? w->d_idx2 : w->d_idx, sizeof(int32_t) * n_rays,
+                                cudaMemcpyDeviceToHost, w->copy_stream));
+    if (ranges_out != NULL || hit_idx_out != NULL) {
+      UMRS_CUDA(cudaEventRecord(w->buf_free[buf], w->copy_stream));
+      w->buf_busy[buf] = true;
+      w->async_pending = true;
+    }
+    UMRS_CUDA(cudaEventRecord(w->tick_done[w->async_ticks & 3], w->copy_stream));
+    w->async_ticks += 1;
+    return UMRS_OK;
   }
+  // blocking tick: 8 slices (first-slice latency matters) -- measured on B200
   int n_slices = 1;
-  if (ranges_out != NULL && w->W >= 1024) n_slices = pipelined ? 4 : 8;
+  if (ranges_out != NULL && w->W >= 1024) n_slices = 8;
   if (g_tuning.step_slices > 0) n_slices = g_tuning.step_slices;   // umrs_tuning_set("step_slices")
   if (n_slices > w->W) n_slices = w->W;
-  if (n_slices > kMaxSlices - 1) n_slices = kMaxSlices - 1;
+  if (n_slices > kMaxSlices) n_slices = kMaxSlices;
   const size_t rpw = (size_t)w->rays_per_world;
-  // Copies of the previous pipelined tick may still be reading d_ranges / d_idx.  Sliced the same
-  // way, slice s only has to wait for the previous copy of slice s; otherwise (another slice
-  // count, or a tick without outputs, which runs as one launch) everything waits for all of them.
-  const bool same_slicing = w->async_pending && n_slices == w->pending_slices;
-  if (w->async_pending && !same_slicing)
-    for (int s = 0; s < w->pending_slices; ++s) UMRS_CUDA(cudaStreamWaitEvent(w->stream, w->copy_done[s], 0));
   for (int s = 0; s < n_slices; ++s) {
     const int32_t first = (int32_t)((int64_t)w->W * s / n_slices);
     const int32_t end = (int32_t)((int64_t)w->W * (s + 1) / n_slices);
-    if (same_slicing) UMRS_CUDA(cudaStreamWaitEvent(w->stream, w->copy_done[s], 0));
-    int st = world_launch(w, dc, dm, w->stream, first, end - first, s == n_slices - 1);
+    int st = world_launch(w, dc, dm, w->stream, first, end - first, s == n_slices - 1, 0);
     if (st != UMRS_OK) return st;
     if (ranges_out == NULL && hit_idx_out == NULL) continue;
     UMRS_CUDA(cudaEventRecord(w->slice_done[s], w->stream));
@@ -540,20 +579,6 @@ static int step_enqueue(umrs_world* w, const float* cmds, const uint8_t* cmd_mas
     if (hit_idx_out)
       UMRS_CUDA(cudaMemcpyAsync(hit_idx_out + off, w->d_idx + off, sizeof(int32_t) * cnt,
                                 cudaMemcpyDeviceToHost, w->copy_stream));
-    if (pipelined) UMRS_CUDA(cudaEventRecord(w->copy_done[s], w->copy_stream));
-  }
-  if (pipelined) {
-    // the tick is complete when its kernels AND its copies are
-    UMRS_CUDA(cudaEventRecord(w->kernels_done, w->stream));
-    UMRS_CUDA(cudaStreamWaitEvent(w->copy_stream, w->kernels_done, 0));
-    UMRS_CUDA(cudaEventRecord(w->tick_done[w->async_ticks & 3], w->copy_stream));
-    w->async_ticks += 1;
-    if (ranges_out != NULL || hit_idx_out != NULL) {
-      w->async_pending = true;
-      w->pending_slices = n_slices;
-    }
-    // (a tick without outputs waited for the earlier copies above and starts none: what was
-    // pending stays pending until a wait call)
   }
   return UMRS_OK;
 }
@@ -567,6 +592,7 @@ int umrs_world_step(umrs_world* w, const float* cmds, const uint8_t* cmd_mask,
   UMRS_CUDA(cudaStreamSynchronize(w->stream));
   UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
   w->async_pending = false;
+  w->buf_busy[0] = w->buf_busy[1] = false;
   if (w->plan.kernel == 1) return capi_read_flags(w->d_flags);   // only the grid walk can raise one
   return UMRS_OK;
 }
@@ -630,6 +656,7 @@ int umrs_world_set_state(umrs_world* w, const void* blob, uint64_t bytes) {
   }
   UMRS_CUDA(cudaDeviceSynchronize());
   w->async_pending = false;
+  w->buf_busy[0] = w->buf_busy[1] = false;
   const unsigned char* p = static_cast<const unsigned char*>(blob) + sizeof(h);
   const size_t WR = (size_t)w->W * w->R;
   const size_t nr = sizeof(RobotState) * WR, nh = sizeof(HumanState) * (size_t)w->W * w->H;
@@ -669,14 +696,15 @@ int umrs_world_wait(umrs_world* w) {
   UMRS_CUDA(cudaStreamSynchronize(w->stream));
   UMRS_CUDA(cudaStreamSynchronize(w->copy_stream));
   w->async_pending = false;
+  w->buf_busy[0] = w->buf_busy[1] = false;
   return UMRS_OK;
 }
 
 int umrs_world_device_buffers(umrs_world* w, float** ranges_dev, int32_t** hit_idx_dev,
                               float** robot_pose_dev) {
   if (w == NULL) return UMRS_ERR_INVALID;
-  if (ranges_dev) *ranges_dev = w->d_ranges;
-  if (hit_idx_dev) *hit_idx_dev = w->d_idx;
+  if (ranges_dev) *ranges_dev = w->out_buf ? w->d_ranges2 : w->d_ranges;
+  if (hit_idx_dev) *hit_idx_dev = w->out_buf ? w->d_idx2 : w->d_idx;
   if (robot_pose_dev) *robot_pose_dev = w->d_pose;
   return UMRS_OK;
 }
@@ -740,7 +768,7 @@ int umrs_world_stats(umrs_world* w, double* out4) {
   memcpy(&init[1], &inf_bits, sizeof(double));
   UMRS_CUDA(cudaDeviceSynchronize());  // the last step may have run on a caller stream
   UMRS_CUDA(cudaMemcpyAsync(w->d_stats, init, sizeof(init), cudaMemcpyHostToDevice, w->stream));
-  UMRS_CUDA(launch_stats(w->d_ranges, (size_t)w->W * w->rays_per_world, w->d_stats, w->stream));
+  UMRS_CUDA(launch_stats(w->out_buf ? w->d_ranges2 : w->d_ranges, (size_t)w->W * w->rays_per_world, w->d_stats, w->stream));
   double raw[4];
   UMRS_CUDA(cudaMemcpyAsync(raw, w->d_stats, sizeof(raw), cudaMemcpyDeviceToHost, w->stream));
   UMRS_CUDA(cudaStreamSynchronize(w->stream));
