@@ -201,6 +201,29 @@ def test_reference_render_worlds_draw_the_same_noise_as_default_worlds():
 
 
 @pytest.mark.gpu
+def test_gpu_reference_render_picket_fence_overflows_the_speculative_staging(ref):
+    """A long wall behind 70 posts: the wall is split 70 times (every post pushes a piece onto the list being
+    iterated, vector_map.cpp:174), far more than the 32 pieces a speculative candidate may stage, so the
+    CTA-per-fan form has to give the round up and redo the wall in order; walls in front of and behind it
+    exercise the commit order.  Both forms must return the reference's bits."""
+    import ut_multirobot_sim_b200 as umrs
+    posts = [[x, 5.0, x + 0.12, 5.0] for x in np.linspace(-14, 14, 70)]
+    raw = np.array([[-3, 2.5, 3, 2.6]] + posts + [[-20, 9.0, 20, 9.3], [-25, 12.0, 25, 12.0], [-6, 7.0, -2, 7.2]], np.float32)
+    segs = umrs.map_cleanup(raw)
+    vmap = umrs.VectorMap(lines=segs)
+    rm = ref.map_from_segments(segs, False)
+    rng = np.random.default_rng(3)
+    poses = np.stack([rng.uniform(-4, 4, 1200), rng.uniform(-3, 2, 1200), rng.uniform(0.6, 2.5, 1200)], 1).astype(np.float32)
+    fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - D135, poses[:, 2] + D135], 1).astype(np.float32)
+    want = rm.scan_batch(fans, 0.4, 100.0, 1081, threads=4)
+    big = vmap.ScanBatchReferenceRender(fans, 100.0, 1081)              # 1200 fans: warp per fan
+    small = np.concatenate([vmap.ScanBatchReferenceRender(fans[k:k + 400], 100.0, 1081) for k in range(0, 1200, 400)])
+    assert np.array_equal(big.view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(small.view(np.uint32), want.view(np.uint32))
+    assert (want < 8.0).mean() > 0.1 and (want > 8.5).mean() > 0.1    # rays end on posts and, between them, on the wall
+
+
+@pytest.mark.gpu
 def test_gpu_reference_render_warp_per_fan_and_cta_per_fan_forms_agree(ref):
     """Big batches take the warp-per-fan kernel, small ones the CTA-per-fan kernel: same bits,
     and the reference's on a sample."""

@@ -81,6 +81,7 @@ struct Tuning {
   int grid_from = 0;
   int step_slices = 0;
   int tma_stage = -1;   // -1 auto (the plan decides), 0 off, 1 on wherever the plan allows it
+  int render_cta_fans = 0;   // reference render: batches up to this many fans run one 4-warp CTA per fan (0 = default)
 };
 extern Tuning g_tuning;
 
@@ -175,7 +176,7 @@ struct RenderScanParams {
   uint32_t key0, key1, step_lo, step_hi;
   int32_t world_base;
 };
-constexpr int kRenderScratchCWords = 2000 + 2 * 2000 + 1000;   // per fan: float c[2000], uint2 iv[2000], u16 list[2000]
+constexpr int kRenderScratchCWords = 2000 + 2 * 2000 + 4 * 1000;   // per fan: float c[2000], uint2 iv[2000], 4 x u16 list[2000]
 constexpr int kRenderFansPerLaunch = 4096;   // 295 MB of scratch; ~1.15 resident waves of warps on 148 SMs
 cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, int fan_end,
                                     cudaStream_t stream);

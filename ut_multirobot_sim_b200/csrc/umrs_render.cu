@@ -166,10 +166,11 @@ struct SceneStore {
   int cap;
   uint2* gl_iv;
   uint16_t* gl_list;
+  int list_cap;    // list entries kept in shared memory
   __device__ __forceinline__ uint2 ld_iv(int j) const { return j < cap ? iv[j] : gl_iv[j]; }
   __device__ __forceinline__ void st_iv(int j, uint2 v) const { if (j < cap) iv[j] = v; else gl_iv[j] = v; }
-  __device__ __forceinline__ int ld_list(int k) const { return (int)(k < cap ? list[k] : gl_list[k]); }
-  __device__ __forceinline__ void st_list(int k, int j) const { if (k < cap) list[k] = (uint16_t)j; else gl_list[k] = (uint16_t)j; }
+  __device__ __forceinline__ int ld_list(int k) const { return (int)(k < list_cap ? list[k] : gl_list[k]); }
+  __device__ __forceinline__ void st_list(int k, int j) const { if (k < list_cap) list[k] = (uint16_t)j; else gl_list[k] = (uint16_t)j; }
   __device__ __forceinline__ Seg ld(int j) const { return load_seg(j < cap ? sm + j : gl + j); }
   __device__ __forceinline__ void st(int j, const Seg& t) const { store_seg(j < cap ? sm + j : gl + j, t); }
   __device__ __forceinline__ float4 ld_cast(int j) const { return j < cap ? sm[j] : gl[j]; }
@@ -182,9 +183,26 @@ struct SceneStore {
 // One fan, rendered by a group of kW warps (threads gt = 0 .. 32 kW - 1 of the caller's CTA).
 // `slot` picks the fan's global scratch; sm / sm_c / iv / list are the group's kSceneSmem * kW
 // shared-memory entries.
-template <int kW>
+// Speculative form (kSpec, kW = 4): most candidate lines -- 85 % on a floor plan -- end up completely
+// occluded and leave the scene exactly as they found it, so the NEXT candidates' trims by the scene
+// do not depend on them.  Each of the four warps therefore takes one of four consecutive candidates
+// and trims it by the same scene snapshot (warp-level loops, own candidate list); the results are
+// then committed in candidate order: the pieces a candidate split off are appended to the list
+// (warp 0 appends directly -- its snapshot is the true scene -- the others stage theirs), and the
+// first candidate that survives stops the round: the whole CTA trims the scene by it (:237-240),
+// appends it, and the candidates behind it are redone against the new scene.  Same events, same
+// order as the sequential loop, hence the same bits (tests/test_render.py).
+constexpr int kStageMax = 32;      // pieces a speculative candidate may split off before it is redone in order
+struct SpecShared {
+  float4 stage[kRenderWarpsPerCta][kStageMax];
+  float4 cur[kRenderWarpsPerCta];
+  int alive[kRenderWarpsPerCta], npush[kRenderWarpsPerCta], valid[kRenderWarpsPerCta], nlist[kRenderWarpsPerCta];
+};
+
+template <int kW, bool kSpec = false>
 __device__ void render_fan(const RenderScanParams& p, int f, int slot, GroupShared* gs, float4* sm,
-                           float* sm_c, uint2* iv, uint16_t* list) {
+                           float* sm_c, uint2* iv, uint16_t* list, SpecShared* ss = nullptr) {
+  static_assert(!kSpec || kW == kRenderWarpsPerCta, "the speculative form is one 4-warp CTA per fan");
   constexpr int kGroup = 32 * kW;                        // threads per fan
   const int gt = (int)threadIdx.x % kGroup;              // thread index inside the group
   float4* lines = p.scratch_lines + (size_t)slot * render::kRenderMaxLines;
@@ -200,6 +218,7 @@ __device__ void render_fan(const RenderScanParams& p, int f, int slot, GroupShar
   scene.gl_c = blk;
   scene.gl_iv = reinterpret_cast<uint2*>(blk + render::kRenderMaxLines);
   scene.gl_list = reinterpret_cast<uint16_t*>(blk + 3 * render::kRenderMaxLines);
+  scene.list_cap = scene.cap;
   const float4 fp = p.fans[f];
   V2 loc;
   loc.x = fp.x; loc.y = fp.y;
@@ -250,6 +269,115 @@ __device__ void render_fan(const RenderScanParams& p, int f, int slot, GroupShar
 
   // ---- SceneRender, vector_map.cpp:226-246 ---------------------------------------------
   int n_scene = 0;
+  if constexpr (kSpec) {
+    const int warp = gt >> 5, lane = gt & 31;
+    uint16_t* gl_lists = reinterpret_cast<uint16_t*>(blk + 3 * render::kRenderMaxLines);   // 4 x u16[2000]
+    SceneStore sw = scene;             // this warp's view: its own candidate list
+    sw.list = list + warp * kSceneSmem;
+    sw.list_cap = kSceneSmem;
+    sw.gl_list = gl_lists + warp * render::kRenderMaxLines;
+    int i = 0;
+    while (i < n_lines && i < render::kRenderMaxLines) {
+      const int lim = n_lines < render::kRenderMaxLines ? n_lines : render::kRenderMaxLines;
+      const int n_avail = lim - i < kRenderWarpsPerCta ? lim - i : kRenderWarpsPerCta;
+      if (warp < n_avail) {
+        Seg cur = load_seg(lines + i + warp);
+        const uint2 iv_cur = seg_interval(loc, cur);
+        int n_list = 0;
+        for (int b = 0; b < n_scene; b += 32) {
+          const int j = b + lane;
+          const bool keep = j < n_scene && intervals_may_touch(iv_cur, scene.ld_iv(j));
+          int total;
+          const int pos = group_append_pos<1>(gs, keep, n_list, &total);
+          if (keep) sw.st_list(pos, j);
+          n_list += total;
+        }
+        __syncwarp();
+        int npush = 0, k0 = 0;
+        bool valid = true;
+        while (k0 < n_list && render::sq_length(cur) >= render::kRenderEps) {     // :231
+          const int k = k0 + lane;
+          Seg mine = cur, piece;
+          piece.p0.x = piece.p0.y = piece.p1.x = piece.p1.y = 0.f;
+          bool pushed = false, acts = false;
+          if (k < n_list) {
+            const Seg t = scene.ld(sw.ld_list(k));
+            if (!(render::sq_length(t) < render::kRenderEps)) {                 // :232
+              pushed = render::trim_occlusion(loc, t, &mine, &piece);
+              acts = pushed || !same_bits(mine, cur);
+            }
+          }
+          const int first = group_first<1>(gs, acts);
+          if (first < 0) { k0 += 32; continue; }
+          cur = shfl_seg(mine, first);
+          if (__shfl_sync(0xffffffffu, pushed ? 1 : 0, first) != 0) {
+            if (warp == 0) {     // the first candidate of a round sees the true scene: append directly (:174)
+              if (lane == first && n_lines + npush < render::kRenderMaxLines) store_seg(lines + n_lines + npush, piece);
+            } else {
+              if (npush >= kStageMax) { valid = false; break; }   // redone in order, as warp 0 of a later round
+              if (lane == first) ss->stage[warp][npush] = make_float4(piece.p0.x, piece.p0.y, piece.p1.x, piece.p1.y);
+            }
+            ++npush;
+          }
+          k0 += first + 1;
+        }
+        if (lane == 0) {
+          ss->cur[warp] = make_float4(cur.p0.x, cur.p0.y, cur.p1.x, cur.p1.y);
+          ss->alive[warp] = render::sq_length(cur) > render::kRenderEps ? 1 : 0;   // :236
+          ss->npush[warp] = npush;
+          ss->valid[warp] = valid ? 1 : 0;
+          ss->nlist[warp] = n_list;
+        }
+      }
+      __syncthreads();
+      // ---- commit, in candidate order (block-uniform decisions) ----
+      int adv = 0;
+      for (int w = 0; w < n_avail; ++w) {
+        if (w > 0 && !ss->valid[w]) break;
+        const int np = ss->npush[w];
+        if (w > 0)
+          for (int k = gt; k < np; k += kGroup)
+            if (n_lines + k < render::kRenderMaxLines) lines[n_lines + k] = ss->stage[w][k];
+        n_lines += np;
+        adv = w + 1;
+        if (ss->alive[w]) {
+          // the survivor trims the scene (:237-240) -- the whole CTA, over the survivor's own list -- and joins it
+          SceneStore sb = scene;
+          sb.list = list + w * kSceneSmem;
+          sb.list_cap = kSceneSmem;
+          sb.gl_list = gl_lists + w * render::kRenderMaxLines;
+          const Seg cur = load_seg(&ss->cur[w]);
+          const int n_it = ss->nlist[w];
+          for (int b = 0; b < n_it; b += kGroup) {
+            const int k = b + gt;
+            Seg piece;
+            piece.p0.x = piece.p0.y = piece.p1.x = piece.p1.y = 0.f;
+            bool pushed = false;
+            if (k < n_it) {
+              const int j = sb.ld_list(k);
+              Seg t = scene.ld(j);
+              if (!(render::sq_length(t) < render::kRenderEps)) {               // :238
+                pushed = render::trim_occlusion(loc, cur, &t, &piece);
+                scene.st(j, t);
+              }
+            }
+            int total;
+            const int pos = group_append_pos<kW>(gs, pushed, n_lines, &total);
+            if (pushed && pos < render::kRenderMaxLines) store_seg(lines + pos, piece);
+            n_lines += total;
+          }
+          if (gt == 0) {
+            scene.st(n_scene, cur);
+            scene.st_iv(n_scene, seg_interval(loc, cur));
+          }
+          ++n_scene;
+          break;
+        }
+      }
+      i += adv;
+      __syncthreads();
+    }
+  } else {
   // the candidate list is read one entry ahead: entries below n_lines never change (pieces are
   // appended at n_lines and beyond), so a prefetched entry is valid iff it existed when it was read
   Seg ahead;
@@ -339,6 +467,7 @@ __device__ void render_fan(const RenderScanParams& p, int f, int slot, GroupShar
     }
     group_sync<kW>();
   }
+  }   // !kSpec
 
   // ---- LineCast list, :439-456 (ordered; built in place over the scene: a trip's entries are
   // all read before any of its casts is written, and cast positions never run ahead of the trip) ----
@@ -406,9 +535,10 @@ k_scan_reference_render(const RenderScanParams p) {
   __shared__ float scene_sm_c[kRenderWarpsPerCta * kSceneSmem];
   __shared__ uint2 scene_iv[kRenderWarpsPerCta * kSceneSmem];
   __shared__ uint16_t scene_list[kRenderWarpsPerCta * kSceneSmem];
+  __shared__ SpecShared ss;
   const int slot = (int)blockIdx.x;
   if (slot >= p.n_fans) return;
-  render_fan<kRenderWarpsPerCta>(p, p.fan_begin + slot, slot, &gs, scene_sm, scene_sm_c, scene_iv, scene_list);
+  render_fan<kRenderWarpsPerCta, true>(p, p.fan_begin + slot, slot, &gs, scene_sm, scene_sm_c, scene_iv, scene_list, &ss);
 }
 
 // ---- big batches: one 1-warp CTA per fan; 28 CTAs per SM = 4144 resident fans, so that a 4096-fan
@@ -431,7 +561,7 @@ cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, in
   RenderScanParams q = p;
   q.fan_begin = fan_begin;            // the launch covers fans [fan_begin, fan_end)
   q.n_fans = fan_end - fan_begin;
-  if (q.n_fans <= kRenderCtaPerFanUpTo) {
+  if (q.n_fans <= (g_tuning.render_cta_fans > 0 ? g_tuning.render_cta_fans : kRenderCtaPerFanUpTo)) {
     // few fans: a whole CTA per fan (latency)
     k_scan_reference_render<<<q.n_fans, 32 * kRenderWarpsPerCta, 0, stream>>>(q);
     note_launch();
