@@ -216,7 +216,7 @@ def config4(iters=100):
                                  "(vector_map.cpp:223,229,248); the map alone is 100k segments"}
 
 
-def reference_render(maps=(256, 1024), batches=(1, 64, 4096), iters=5, cpu=True):
+def reference_render(maps=(256, 1024), batches=(1, 64, 4096, 16384), iters=5, cpu=True):
     """The opt-in reference render (bit-identical to the reference's GetPredictedScan), device buffers."""
     outs = []
     for M in maps:

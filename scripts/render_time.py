@@ -9,8 +9,8 @@ d135 = np.float32(np.pi * 135.0 / 180.0)
 M = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 segs = umrs.map_cleanup(synth.floorplan_segments(M, extent=200.0, seed=1234))
 vmap = umrs.VectorMap(lines=segs)
-poses_all = synth.sample_free_poses_fast(segs, 8192, 200.0, seed=11)
-for W in (1, 64, 512, 1024, 2048, 4096, 8192):
+poses_all = synth.sample_free_poses_fast(segs, 16384, 200.0, seed=11)
+for W in (1, 512, 4096, 8192, 16384):
     poses = poses_all[:W]
     fans = np.stack([poses[:, 0], poses[:, 1], poses[:, 2] - d135, poses[:, 2] + d135], 1).astype(np.float32)
     d_fans = torch.from_numpy(fans).cuda()

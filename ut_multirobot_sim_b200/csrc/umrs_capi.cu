@@ -123,6 +123,7 @@ struct umrs_map {
   float4* d_render_lines = nullptr;
   float4* d_render_scene = nullptr;
   float* d_render_c = nullptr;
+  int32_t render_cap = 0;          // fans the scratch holds
 };
 
 // Host-side, one-time (like VectorMap::Load/Cleanup): bin every segment by the
@@ -556,19 +557,31 @@ int umrs_scan_batch_reference_render_device(umrs_map* m, const float* obj_segs_d
       (n_fans > 0 && fans_dev == NULL) || (n_obj > 0 && obj_segs_dev == NULL))
     return UMRS_ERR_INVALID;
   if (n_fans == 0) return UMRS_OK;
-  if (m->d_render_c == nullptr) {   // all three or none
-    const size_t n = (size_t)kRenderFansPerLaunch * 2000;
+  // scratch for one launch: 104 KB per fan, sized to what this map has been asked for so far
+  const int32_t want = n_fans < kRenderFansPerLaunch ? n_fans : kRenderFansPerLaunch;
+  if (m->render_cap < want) {
+    cudaStream_t s0 = stream ? (cudaStream_t)stream : m->stream;
+    UMRS_CUDA(cudaStreamSynchronize(s0));   // an earlier launch may still use the old scratch
+    if (m->d_render_lines) cudaFree(m->d_render_lines);
+    if (m->d_render_scene) cudaFree(m->d_render_scene);
+    if (m->d_render_c) cudaFree(m->d_render_c);
+    m->d_render_lines = m->d_render_scene = nullptr;
+    m->d_render_c = nullptr;
+    m->render_cap = 0;
+    const int32_t cap = want < 1024 ? 1024 : want;
+    const size_t n = (size_t)cap * 2000;
     float4 *a = nullptr, *b = nullptr;
     float* c = nullptr;
     cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&a), sizeof(float4) * n);
     if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&b), sizeof(float4) * n);
-    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&c), sizeof(float) * ((size_t)kRenderFansPerLaunch * kRenderScratchCWords));
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&c), sizeof(float) * ((size_t)cap * kRenderScratchCWords));
     if (e != cudaSuccess) {
       if (a) cudaFree(a);
       if (b) cudaFree(b);
       return cuda_fail(e, "reference render scratch");
     }
     m->d_render_lines = a; m->d_render_scene = b; m->d_render_c = c;
+    m->render_cap = cap;
   }
   RenderScanParams p;
   memset(&p, 0, sizeof(p));
@@ -585,8 +598,8 @@ int umrs_scan_batch_reference_render_device(umrs_map* m, const float* obj_segs_d
   p.scratch_scene = m->d_render_scene;
   p.scratch_c = m->d_render_c;
   cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
-  for (int b = 0; b < n_fans; b += kRenderFansPerLaunch)   // stream order: one scratch, reused
-    UMRS_CUDA(launch_reference_render(p, b, b + kRenderFansPerLaunch < n_fans ? b + kRenderFansPerLaunch : n_fans, st));
+  for (int b = 0; b < n_fans; b += m->render_cap)   // stream order: one scratch, reused
+    UMRS_CUDA(launch_reference_render(p, b, b + m->render_cap < n_fans ? b + m->render_cap : n_fans, st));
   return UMRS_OK;
 }
 

@@ -177,7 +177,7 @@ struct RenderScanParams {
   int32_t world_base;
 };
 constexpr int kRenderScratchCWords = 2000 + 2 * 2000 + 4 * 1000;   // per fan: float c[2000], uint2 iv[2000], 4 x u16 list[2000]
-constexpr int kRenderFansPerLaunch = 4096;   // 295 MB of scratch; ~1.15 resident waves of warps on 148 SMs
+constexpr int kRenderFansPerLaunch = 16384;  // 1.7 GB of scratch (104 KB per fan); 4144 fans are resident at a time, the rest refill the SMs as fans finish
 cudaError_t launch_reference_render(const RenderScanParams& p, int fan_begin, int fan_end,
                                     cudaStream_t stream);
 

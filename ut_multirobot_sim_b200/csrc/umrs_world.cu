@@ -90,6 +90,7 @@ struct umrs_world {
   float4* d_render_lines = nullptr;
   float4* d_render_scene = nullptr;
   float* d_render_c = nullptr;
+  int32_t render_cap = 0;   // fans the render scratch holds (one launch)
   bool counters_on = false;
   double* d_stats = nullptr;
   uint32_t* d_flags = nullptr;   // sticky device-side conditions (kFlagRowsTruncated)
@@ -244,9 +245,10 @@ int umrs_world_create(umrs_map* map, const umrs_world_desc* d, umrs_world** out)
   if (ok()) e = dalloc(&w->d_mask, WR);
   if (ok()) e = dalloc(&w->d_ranges, n_rays);
   if (ok() && d->write_hit_idx && !d->reference_render) e = dalloc(&w->d_idx, n_rays);
-  if (ok() && d->reference_render) e = dalloc(&w->d_render_lines, (size_t)kRenderFansPerLaunch * 2000);
-  if (ok() && d->reference_render) e = dalloc(&w->d_render_scene, (size_t)kRenderFansPerLaunch * 2000);
-  if (ok() && d->reference_render) e = dalloc(&w->d_render_c, (size_t)kRenderFansPerLaunch * kRenderScratchCWords);
+  w->render_cap = (int32_t)(WR < (size_t)kRenderFansPerLaunch ? WR : (size_t)kRenderFansPerLaunch);
+  if (ok() && d->reference_render) e = dalloc(&w->d_render_lines, (size_t)w->render_cap * 2000);
+  if (ok() && d->reference_render) e = dalloc(&w->d_render_scene, (size_t)w->render_cap * 2000);
+  if (ok() && d->reference_render) e = dalloc(&w->d_render_c, (size_t)w->render_cap * kRenderScratchCWords);
   if (ok()) e = dalloc(&w->d_fan_params, WR);
   if (ok()) e = dalloc(&w->d_obj_lines, (size_t)w->W * w->L_obj);
   if (ok()) e = dalloc(&w->d_pose, WR * 3);
@@ -468,8 +470,8 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
     q.key0 = p.key0; q.key1 = p.key1; q.step_lo = p.step_lo; q.step_hi = p.step_hi;
     q.world_base = w->desc.world_index_base;
     const int f0 = first * w->R, f1 = (first + count) * w->R;
-    for (int b = f0; b < f1; b += kRenderFansPerLaunch)
-      UMRS_CUDA(launch_reference_render(q, b, b + kRenderFansPerLaunch < f1 ? b + kRenderFansPerLaunch : f1, stream));
+    for (int b = f0; b < f1; b += w->render_cap)
+      UMRS_CUDA(launch_reference_render(q, b, b + w->render_cap < f1 ? b + w->render_cap : f1, stream));
   }
   if (last) {
     w->cur ^= 1;
