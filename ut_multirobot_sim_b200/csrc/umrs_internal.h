@@ -144,6 +144,8 @@ struct WorldStepParams {
   int32_t world_base;
   int32_t laser_noise, motion_noise;
   int32_t skip_scan;         // stop after the entity steps / object lines / fan (reference render follows)
+  int32_t cars_only;         // every robot is an Ackermann car and there are no humans: the kernel instance
+                             // without the other models' code is launched
 };
 
 // Opt-in reference render (umrs_render.cu): one warp per fan, scratch for the fans of ONE launch.

@@ -1017,8 +1017,12 @@ __device__ __forceinline__ int signf_(float v) { return (0.0f < v) - (v < 0.0f);
 
 // DriveCallback of each model: ackermann_model.cpp:41-50,
 // diff_drive_model.cpp:170-197, omnidirectional_model.cpp:49-58.
+// kCarsOnly: the roster holds Ackermann cars only (the launcher checked), so the other models'
+// code is not even compiled into this instance -- the kernel's instruction footprint is what its
+// no_instruction stalls pay for (same-box A/B: +1.5 % on the bench workload).
+template <bool kCarsOnly>
 __device__ void robot_command(RobotState& s, const umrs_robot_params& p, const float* cmd) {
-  if (p.model_type == UMRS_ACKERMANN_DRIVE) {
+  if (kCarsOnly || p.model_type == UMRS_ACKERMANN_DRIVE) {
     if (!isfinite(cmd[0]) || !isfinite(cmd[1])) return;
     s.cmd[0] = cmd[0]; s.cmd[1] = cmd[1]; s.cmd[2] = 0.f;
     s.cmd_age = 0;
@@ -1053,9 +1057,10 @@ __device__ void accel_limit(double& v, float target, float pos_lim, float neg_li
   }
 }
 
+template <bool kCarsOnly>
 __device__ void robot_step(RobotState& s, const umrs_robot_params& p, double dt, float n1, float n2) {
   const bool stale = (double)s.cmd_age * dt > 0.1;  // kMaxCommandAge in sim time
-  if (p.model_type == UMRS_ACKERMANN_DRIVE) {
+  if (kCarsOnly || p.model_type == UMRS_ACKERMANN_DRIVE) {
     // ackermann_model.cpp:52-96
     if (stale) s.cmd[0] = 0.f;
     const float vel = s.vel[0];
@@ -1177,7 +1182,7 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
 // CTA alone writes the "out" state (ping-pong buffers).  Order as in
 // Simulator::Run (simulator.cpp:531-541): update() first, scan from the
 // post-step pose against the post-step object lines.
-template <int kThreads, int kCtas>
+template <int kThreads, int kCtas, bool kCarsOnly>
 __global__ void __launch_bounds__(kThreads, kCtas)
 k_world_step(const __grid_constant__ WorldStepParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1201,7 +1206,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
     if (e < p.O) {
       const float* sp = p.static_pose + ((size_t)w * p.O + e) * 3;
       px = sp[0]; py = sp[1]; pth = sp[2];
-    } else if (e < p.O + p.H) {
+    } else if (!kCarsOnly && e < p.O + p.H) {
       const int h = e - p.O;
       HumanState s = p.hs_in[(size_t)w * p.H + h];
       human_step(s, p.humans[h], dt);
@@ -1214,10 +1219,10 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
       const umrs_robot_params& rp = p.robots[rr];
       if (p.cmds != nullptr && (p.cmd_mask == nullptr || p.cmd_mask[gi] != 0)) {
         const float cmd[3] = {p.cmds[gi * 3 + 0], p.cmds[gi * 3 + 1], p.cmds[gi * 3 + 2]};
-        robot_command(s, rp, cmd);
+        robot_command<kCarsOnly>(s, rp, cmd);
       }
       float n1 = 0.f, n2 = 0.f;
-      if (p.motion_noise && rp.model_type == UMRS_ACKERMANN_DRIVE) {
+      if (p.motion_noise && (kCarsOnly || rp.model_type == UMRS_ACKERMANN_DRIVE)) {
         const uint4 wd = philox4x32(
             make_uint4(0u, (uint32_t)(p.world_base + w) * (uint32_t)p.R + (uint32_t)rr,
                        p.step_lo, p.step_hi ^ kStreamMotion),
@@ -1225,7 +1230,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
         const float2 g = box_muller(wd.x, wd.y);
         n1 = g.x; n2 = g.y;
       }
-      robot_step(s, rp, dt, n1, n2);
+      robot_step<kCarsOnly>(s, rp, dt, n1, n2);
       if (owner) {
         p.rs_out[gi] = s;
         if (p.robot_pose_out != nullptr) {
@@ -1371,7 +1376,7 @@ static cudaError_t dev_limits(DevLimits** out) {
 template <int kThreads, int kCtas>
 static bool seats(size_t smem) {
   int n = 0, m = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kThreads, kCtas>, kThreads, smem) != cudaSuccess ||
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kThreads, kCtas, false>, kThreads, smem) != cudaSuccess ||
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_scan_batch<kThreads, kCtas>, kThreads, smem) != cudaSuccess) {
     (void)cudaGetLastError();
     return false;
@@ -1413,7 +1418,10 @@ static cudaError_t configure_shape(DevLimits& d, int shape, size_t smem_bytes) {
   cudaError_t e = cudaFuncSetAttribute(k_scan_batch<kThreads, kCtas>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas>,
+  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, false>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, true>,
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
   d.configured[shape] = smem_bytes;
@@ -1434,7 +1442,9 @@ static cudaError_t launch_step_shape(DevLimits& d, int shape, const WorldStepPar
                                      size_t smem, cudaStream_t stream) {
   cudaError_t e = configure_shape<kThreads, kCtas>(d, shape, smem);
   if (e != cudaSuccess) return e;
-  k_world_step<kThreads, kCtas><<<fans, kThreads, smem, stream>>>(p);
+  // a roster of Ackermann cars only (and no humans) runs the instance compiled without the other models
+  if (p.cars_only) k_world_step<kThreads, kCtas, true><<<fans, kThreads, smem, stream>>>(p);
+  else k_world_step<kThreads, kCtas, false><<<fans, kThreads, smem, stream>>>(p);
   return cudaSuccess;
 }
 

@@ -444,6 +444,9 @@ static int world_launch(umrs_world* w, const float* cmds_dev, const uint8_t* mas
   if (w->counters_on && first == 0)
     UMRS_CUDA(cudaMemsetAsync(w->d_counters, 0, sizeof(unsigned long long) * kNumCounters, stream));
   p.skip_scan = w->desc.reference_render ? 1 : 0;
+  p.cars_only = w->H == 0 ? 1 : 0;
+  for (const umrs_robot_params& rp : w->robots)
+    if (rp.model_type != UMRS_ACKERMANN_DRIVE) p.cars_only = 0;
   UMRS_CUDA(launch_world_step(p, stream));
   if (w->desc.reference_render) {
     // the scans: the reference's own render over this launch's fans, on the fan parameters and
