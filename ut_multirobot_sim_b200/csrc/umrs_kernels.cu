@@ -874,7 +874,10 @@ __device__ void finalise(const SmemView& sm, const Fan& fan, float* __restrict__
 // ---- one fan, all passes --------------------------------------------------------------
 __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan,
                          const float4* obj_segs, int n_obj, int skip_lo, int skip_hi,
-                         float* ranges, int32_t* hit_idx, const PostProcess& post, unsigned stage_parity) {
+                         float* ranges, int32_t* hit_idx, const PostProcess& post, unsigned stage_parity,
+                         unsigned long long* counters) {
+  // `counters`: the launch's work-accounting array, or nullptr -- a compile-time nullptr in the
+  // instances ordinary launches use (kCounters = false), so that none of the accounting code is in them
   UMRS_STAMP_INIT;
   const Lattice L = make_lattice(fan.amin, fan.amax, fan.num_rays);
   const int n_chunks = (fan.num_rays + 31) >> 5;
@@ -903,7 +906,7 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     sm.zmax2[k] = 0x7f800000u;   // +inf; valid across passes (a bound from any candidate holds)
   }
   __syncthreads();
-  UMRS_STAMP(c.counters, 1);
+  UMRS_STAMP(counters, 1);
   const int v_total = sm.row_v0[sm.ctl[kCtlNRows]];
   // Bulk-copy staging: single-pass fans only (the area aliases the per-ray winners, which a
   // multi-pass fan carries from pass to pass).
@@ -926,7 +929,7 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
     const int v1 = v0 + c.cap < v_total ? v0 + c.cap : v_total;
     gather(sm, c.src, fan, obj_segs, skip_lo, skip_hi, v0, v1, staged);
     __syncthreads();
-    UMRS_STAMP(c.counters, 2);
+    UMRS_STAMP(counters, 2);
     if (pass == 0 || sm.ctl[kCtlNCand] > 0) {   // block-uniform: a later pass may be empty
       // S1b pays for itself once S2 would need more than one trip of the CTA
       // (block-uniform: n_cand is settled behind the barrier above)
@@ -938,24 +941,24 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
         __syncthreads();
       }
 #ifdef UMRS_HIST   // dev build: histogram of the candidates S2 prepares per fan -> counters[8..15]
-      if (threadIdx.x == 0 && c.counters != nullptr) {
+      if (threadIdx.x == 0 && counters != nullptr) {
         const int ns = pre ? sm.ctl[kCtlNSurv] : sm.ctl[kCtlNCand];
         const int edges[7] = {192, 256, 320, 384, 448, 512, 608};
         int b = 0;
         while (b < 7 && ns > edges[b]) ++b;
-        atomicAdd(c.counters + 8 + b, 1ull);
+        atomicAdd(counters + 8 + b, 1ull);
       }
 #endif
-      make_records(sm, L, pre, c.counters);
+      make_records(sm, L, pre, counters);
       __syncthreads();
-      UMRS_STAMP(c.counters, 3);
+      UMRS_STAMP(counters, 3);
       fill_buckets(sm, K, c.cap / 2, pre);
       __syncthreads();
-      UMRS_STAMP(c.counters, 4);
-      ray_loop(sm, fan, L, K, c.cap / 2, pass, c.multipass != 0, c.counters);
+      UMRS_STAMP(counters, 4);
+      ray_loop(sm, fan, L, K, c.cap / 2, pass, c.multipass != 0, counters);
     }
     __syncthreads();
-    UMRS_STAMP(c.counters, 5);
+    UMRS_STAMP(counters, 5);
     if (v0 + c.cap < v_total) {   // another pass: reset the per-pass state
       if (threadIdx.x < 4) sm.ctl[threadIdx.x] = 0;
       if (threadIdx.x == 4) sm.ctl[kCtlNSurv] = 0;
@@ -963,22 +966,22 @@ __device__ void scan_fan(const SmemView& sm, const ScanCommon& c, const Fan& fan
       __syncthreads();
     }
   }
-  if (c.counters != nullptr && threadIdx.x == 0) {
-    atomicAdd(c.counters + 3, (unsigned long long)pass);
+  if (counters != nullptr && threadIdx.x == 0) {
+    atomicAdd(counters + 3, (unsigned long long)pass);
     // source segments streamed by the gather (16 B each) | source rows, packed: rows << 40
-    atomicAdd(c.counters + 7, (unsigned long long)v_total | ((unsigned long long)sm.ctl[kCtlNRows] << 40));
+    atomicAdd(counters + 7, (unsigned long long)v_total | ((unsigned long long)sm.ctl[kCtlNRows] << 40));
   }
   finalise(sm, fan, ranges, hit_idx, post);
 #ifdef UMRS_PHASE_TIMING
   __syncthreads();
-  UMRS_STAMP(c.counters, 6);
+  UMRS_STAMP(counters, 6);
 #endif
 }
 
 // ---- scan-only kernel (umrs_predicted_scan / umrs_scan_batch) -------------------
 // kThreads x kCtas = the CTA shape and the resident fan CTAs per SM the register budget is
 // held to (see the shape table at the launchers).
-template <int kThreads, int kCtas>
+template <int kThreads, int kCtas, bool kCounters>
 __global__ void __launch_bounds__(kThreads, kCtas)
 k_scan_batch(const __grid_constant__ ScanBatchParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1004,7 +1007,7 @@ k_scan_batch(const __grid_constant__ ScanBatchParams p) {
     const size_t off = (size_t)f * (size_t)p.num_rays;
     __syncthreads();  // previous fan's finalise is done with the best arrays
     scan_fan(sm, p.c, fan, p.obj_segs, p.n_obj, 0, 0, p.c.ranges + off,
-             p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, stage_parity);
+             p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, stage_parity, kCounters ? p.c.counters : nullptr);
   }
 }
 
@@ -1182,7 +1185,7 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
 // CTA alone writes the "out" state (ping-pong buffers).  Order as in
 // Simulator::Run (simulator.cpp:531-541): update() first, scan from the
 // post-step pose against the post-step object lines.
-template <int kThreads, int kCtas, bool kCarsOnly>
+template <int kThreads, int kCtas, bool kCarsOnly, bool kCounters>
 __global__ void __launch_bounds__(kThreads, kCtas)
 k_world_step(const __grid_constant__ WorldStepParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1299,7 +1302,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   const size_t off = (size_t)w * (size_t)p.rays_per_world + (size_t)p.ray_off[r];
   UMRS_STAMP(p.c.counters, 0);
   scan_fan(sm, p.c, fan, sm.obj, p.L_obj, skip_lo, skip_hi, p.c.ranges + off,
-           p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, 0u);
+           p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, 0u, kCounters ? p.c.counters : nullptr);
 }
 
 // ---- K3: statistics of a ranges buffer -------------------------------------------
@@ -1376,8 +1379,8 @@ static cudaError_t dev_limits(DevLimits** out) {
 template <int kThreads, int kCtas>
 static bool seats(size_t smem) {
   int n = 0, m = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kThreads, kCtas, false>, kThreads, smem) != cudaSuccess ||
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_scan_batch<kThreads, kCtas>, kThreads, smem) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kThreads, kCtas, false, false>, kThreads, smem) != cudaSuccess ||
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_scan_batch<kThreads, kCtas, false>, kThreads, smem) != cudaSuccess) {
     (void)cudaGetLastError();
     return false;
   }
@@ -1415,13 +1418,13 @@ static int pick_shape(DevLimits& d, size_t smem, int fans) {
 template <int kThreads, int kCtas>
 static cudaError_t configure_shape(DevLimits& d, int shape, size_t smem_bytes) {
   if (smem_bytes <= d.configured[shape]) return cudaSuccess;
-  cudaError_t e = cudaFuncSetAttribute(k_scan_batch<kThreads, kCtas>,
+  cudaError_t e = cudaFuncSetAttribute(k_scan_batch<kThreads, kCtas, false>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, false>,
+  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, false, false>,
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, true>,
+  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, true, false>,
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
   d.configured[shape] = smem_bytes;
@@ -1433,7 +1436,7 @@ static cudaError_t launch_scan_shape(DevLimits& d, int shape, const ScanBatchPar
                                      cudaStream_t stream) {
   cudaError_t e = configure_shape<kThreads, kCtas>(d, shape, smem);
   if (e != cudaSuccess) return e;
-  k_scan_batch<kThreads, kCtas><<<p.n_fans, kThreads, smem, stream>>>(p);
+  k_scan_batch<kThreads, kCtas, false><<<p.n_fans, kThreads, smem, stream>>>(p);
   return cudaSuccess;
 }
 
@@ -1443,9 +1446,24 @@ static cudaError_t launch_step_shape(DevLimits& d, int shape, const WorldStepPar
   cudaError_t e = configure_shape<kThreads, kCtas>(d, shape, smem);
   if (e != cudaSuccess) return e;
   // a roster of Ackermann cars only (and no humans) runs the instance compiled without the other models
-  if (p.cars_only) k_world_step<kThreads, kCtas, true><<<fans, kThreads, smem, stream>>>(p);
-  else k_world_step<kThreads, kCtas, false><<<fans, kThreads, smem, stream>>>(p);
+  if (p.cars_only) k_world_step<kThreads, kCtas, true, false><<<fans, kThreads, smem, stream>>>(p);
+  else k_world_step<kThreads, kCtas, false, false><<<fans, kThreads, smem, stream>>>(p);
   return cudaSuccess;
+}
+
+// Work accounting on (umrs_*_enable_counters): ONE generic instance per kernel carries the accounting
+// code (256 x 4, every model); the counts do not depend on the CTA shape.
+static size_t g_counted_smem[2] = {0, 0};
+template <typename Kernel, typename Params>
+static cudaError_t launch_counted(Kernel kernel, int which, const Params& p, int ctas, size_t smem, cudaStream_t stream) {
+  if (smem > g_counted_smem[which]) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    g_counted_smem[which] = smem;
+  }
+  kernel<<<ctas, 256, smem, stream>>>(p);
+  note_launch();
+  return cudaGetLastError();
 }
 
 cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) {
@@ -1453,6 +1471,7 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) 
   ScanBatchParams p = p_in;
   const size_t smem = fill_smem_offsets(p.c, 0, 0);
   std::lock_guard<std::mutex> lock(g_dev_mutex);
+  if (p.c.counters != nullptr) return launch_counted(k_scan_batch<256, 4, true>, 0, p, p.n_fans, smem, stream);
   DevLimits* d = nullptr;
   cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;
@@ -1475,6 +1494,7 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
   WorldStepParams p = p_in;
   const size_t smem = fill_smem_offsets(p.c, p.L_obj, p.O + p.H + p.R);
   std::lock_guard<std::mutex> lock(g_dev_mutex);   // the per-device shape cache is shared by all handles
+  if (p.c.counters != nullptr) return launch_counted(k_world_step<256, 4, false, true>, 1, p, fans, smem, stream);
   DevLimits* d = nullptr;
   cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;
