@@ -212,6 +212,27 @@ int umrs_scan_batch_reference_render_device(umrs_map* map, const float* obj_segs
                                             const float* fans_dev, int32_t n_fans, float range_max,
                                             int32_t num_rays, float* ranges_dev, void* stream);
 
+/* The reference render for callers that must not allocate (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernels and the same
+ * bits as umrs_scan_batch_reference_render_device, but the per-fan scratch (104,000 bytes a
+ * fan) lives in a device array compiled into the library instead of cudaMalloc'd memory:
+ *   - at most UMRS_NOALLOC_MAX_FANS fans per call; more returns UMRS_ERR_INVALID (text in
+ *     umrs_last_cuda_error()) and launches nothing.  The array is 6,656,000 bytes, held by
+ *     every GPU that loads the library until the process exits;
+ *   - the call makes no cudaMalloc / cudaFree and calls no allocating routine; map, object
+ *     lines, fans and ranges are the caller's device buffers on the CURRENT device;
+ *   - every call on a device shares the one array: calls that may overlap on the GPU
+ *     (different streams without an ordering between them) RACE.  Order them, e.g. on one
+ *     stream.  Nothing in the array has to start at zero, so calls issue no clear;
+ *   - the first call on a device looks the array's address up (cudaGetSymbolAddress); make
+ *     that call outside stream capture -- n_fans = 0 does the set-up and launches nothing;
+ *   - stream: cudaStream_t as void*, NULL = the legacy default stream; asynchronous. */
+#define UMRS_NOALLOC_MAX_FANS 64
+int umrs_scan_batch_reference_render_noalloc(umrs_map* map, const float* obj_segs_dev, int32_t n_obj,
+                                             const float* fans_dev, int32_t n_fans, float range_max,
+                                             int32_t num_rays, float* ranges_dev, void* stream);
+
 /* ---- batched worlds ------------------------------------------------------------
  * W independent worlds stepping in lockstep; every world has the same robot
  * roster (robots[r] describes robot r of every world), H humans and O static

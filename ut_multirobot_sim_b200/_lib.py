@@ -102,6 +102,8 @@ SIGNATURES = {
     "umrs_scan_batch_reference_render": (C.c_int, [_P, _F, C.c_int32, _F, C.c_int32, C.c_float, C.c_int32, _F]),
     "umrs_scan_batch_reference_render_device": (C.c_int, [_P, _P, C.c_int32, _P, C.c_int32, C.c_float,
                                                           C.c_int32, _P, _P]),
+    "umrs_scan_batch_reference_render_noalloc": (C.c_int, [_P, _P, C.c_int32, _P, C.c_int32, C.c_float,
+                                                           C.c_int32, _P, _P]),
     "umrs_scan_batch": (C.c_int, [_P, _F, C.c_int32, _F, C.c_int32, C.c_float, C.c_int32, _F, _I]),
     "umrs_scan_batch_device": (C.c_int, [_P, _P, C.c_int32, _P, C.c_int32, C.c_float,
                                          C.c_int32, _P, _P, _P]),
