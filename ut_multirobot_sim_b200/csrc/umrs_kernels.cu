@@ -536,8 +536,9 @@ __device__ void precull_mark(const SmemView& sm, const Lattice& L) {
         packed = pack_ranges(chunk_ranges(lo, hi, L));
         const uint32_t bits = __float_as_uint(maxd2);
         const int li = lo + 2 * m + 2, ui = hi - 2 * m - 2;
-        lower_zmax(sm, li, ui, last, n_chunks, bits);
-        lower_zmax(sm, li - L.p_lo, ui - L.p_hi, last, n_chunks, bits);
+#pragma unroll 1
+        for (int img = 0; img < 2; ++img)   // the span and its image one turn down
+          lower_zmax(sm, li - (img ? L.p_lo : 0), ui - (img ? L.p_hi : 0), last, n_chunks, bits);
       }
     }
     float4* r2 = sm.rec + 2 * slot + 1;
@@ -559,6 +560,7 @@ __device__ void precull_compact(const SmemView& sm) {
       if (packed < 0) {
         keep = true;
       } else {
+#pragma unroll 1
         for (int part = 0; part < 2 && !keep; ++part) {
           const int ca = part ? 0 : (packed & 1023);
           const int cb = part ? ((packed >> 20) & 1023) - 1 : ((packed >> 10) & 1023);
@@ -606,8 +608,9 @@ __device__ void make_records(const SmemView& sm, const Lattice& L, bool listed,
             const float t1 = __fmaf_rn(p.z, k.ny, -(p.w * k.nx));
             mind2 = c2 + ((t0 * t1 > 0.f) ? fminf(t0 * t0, t1 * t1) : 0.f);
             const uint32_t bits = __float_as_uint(maxd2);
-            lower_zmax(sm, sp.x + 4, sp.y - 4, last, n_chunks, bits);
-            lower_zmax(sm, sp.x + 4 - L.p_lo, sp.y - 4 - L.p_hi, last, n_chunks, bits);
+#pragma unroll 1
+            for (int img = 0; img < 2; ++img)   // the span and its image one turn down
+              lower_zmax(sm, sp.x + 4 - (img ? L.p_lo : 0), sp.y - 4 - (img ? L.p_hi : 0), last, n_chunks, bits);
           }
         }
       }
@@ -637,6 +640,7 @@ __device__ void fill_buckets(const SmemView& sm, int K, int wide_cap, bool liste
     const int inc = wrap ? 0x10000 : 1;
     const uint16_t entry = (uint16_t)slot;
     bool spilled = false;
+#pragma unroll 1   // one copy of the bucket insertion: the kernel is instruction-fetch sensitive
     for (int part = 0; part < 2; ++part) {
       const int ca = part ? 0 : (packed & 1023);
       const int cb = part ? ((packed >> 20) & 1023) - 1 : ((packed >> 10) & 1023);
