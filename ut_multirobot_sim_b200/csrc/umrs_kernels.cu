@@ -695,6 +695,51 @@ __device__ __forceinline__ unsigned rec_addr(unsigned slot, unsigned rec_s) {
   return a;
 }
 
+// The rarely needed parts of the ray loop, out of line (the kernel is instruction-fetch
+// sensitive: they stay out of the hot loop's cache lines) and on shared-memory addresses only.
+struct RayBest { float q; int slot; int tie; };
+
+// One candidate against this lane's ray, any interval kind.
+__device__ __forceinline__ void test_general(unsigned rec_s, int s, float a, float rx, float ry, RayBest& b) {
+  const unsigned ra = rec_addr((unsigned)s, rec_s);
+  const float4 r4 = lds_f4(ra);
+  const float q = lds_f1_off16(ra) * rcp_approx(__fmaf_rn(r4.z, rx, r4.w * ry));
+  const bool cov = cast_covers(r4.x, r4.y, a);
+  if (cov && q == b.q) b.tie = 1;
+  if (cov && q < b.q) { b.q = q; b.slot = s; }
+}
+
+// The candidates that met a full bucket (list_s = shared address of the wide list), or every slot
+// (list_s = 0), against the chunk's rays, continuing from the running winner b.
+__device__ __noinline__ RayBest slow_candidates(unsigned rec_s, unsigned list_s, int n, float a, float rx,
+                                                float ry, RayBest b) {
+  for (int e = 0; e < n; ++e)
+    test_general(rec_s, list_s ? (int)lds_u16<0>(list_s + 2u * (unsigned)e) : e, a, rx, ry, b);
+  return b;
+}
+
+// Careful sweep after an equal quotient: among the covering candidates with q == best the lowest
+// hit index wins (the reference's scan order with a strict <).  Returns the winner's slot.
+__device__ __noinline__ int tie_sweep(unsigned rec_s, unsigned bucket_s, int K, int n_plain, int n_wrap,
+                                      unsigned list_s, int n_list, float a, float rx, float ry, float best,
+                                      int best_s, int prev_i) {
+  int best_idx = best_s >= 0 ? lds_i1_off20(rec_addr((unsigned)best_s, rec_s)) : prev_i;
+  const int n_b = n_plain + n_wrap;
+  for (int e = 0; e < n_b + n_list; ++e) {
+    int slot;
+    if (e < n_plain) slot = (int)lds_u16<0>(bucket_s + 2u * (unsigned)e);
+    else if (e < n_b) slot = (int)lds_u16<0>(bucket_s + 2u * (unsigned)(K - 1 - (e - n_plain)));
+    else slot = list_s ? (int)lds_u16<0>(list_s + 2u * (unsigned)(e - n_b)) : e - n_b;
+    const unsigned ra = rec_addr((unsigned)slot, rec_s);
+    const float4 r4 = lds_f4(ra);
+    if (!cast_covers(r4.x, r4.y, a)) continue;
+    const float q = lds_f1_off16(ra) * rcp_approx(__fmaf_rn(r4.z, rx, r4.w * ry));
+    const int id = lds_i1_off20(ra);
+    if (q == best && id < best_idx) { best_s = slot; best_idx = id; }
+  }
+  return best_s;
+}
+
 // ---- C: ray loop ----------------------------------------------------------------------
 __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, int K, int wide_cap,
                          int pass, bool multipass, unsigned long long* counters) {
@@ -708,6 +753,7 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
   const float inf = __int_as_float(0x7f800000);
   const unsigned rec_s = (unsigned)__cvta_generic_to_shared(sm.rec);
   const unsigned pool_s = (unsigned)__cvta_generic_to_shared(sm.pool);
+  const unsigned wide_s = (unsigned)__cvta_generic_to_shared(sm.wide);
 
   for (;;) {
     int chunk = 0;
@@ -716,7 +762,6 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
     if (chunk >= n_chunks) break;
     const int i = (chunk << 5) + lane;
     const bool live = i < fan.num_rays;
-    const int cs = chunk << 5, ce = cs + 31;
     float a = __int_as_float(0x7fc00000);  // NaN: covers nothing
     float rx = 0.f, ry = 0.f;
     if (live) {
@@ -777,44 +822,23 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
       bp = bucket_s + 2u * (unsigned)(K - 1);
       for (int e = 0; e < n_wrap; ++e, bp -= 2) UMRS_TEST(lds_u16<0>(bp), UMRS_COV_WRAP)
       n_pairs += n_plain + n_wrap;
-      for (int e = 0; e < n_wide; ++e) {
-        const int ws = sm.wide[e];
-        const float4 w4 = sm.rec[2 * ws];
-        const int2 sp = span_of(w4.x, w4.y, L);
-        if ((sp.x <= ce && sp.y >= cs) || (sp.x - L.p_hi <= ce && sp.y - L.p_lo >= cs)) {
-          UMRS_TEST(ws, cast_covers(r4.x, r4.y, a))
-          ++n_pairs;
-        }
-      }
-    } else {
-      for (int slot = 0; slot < n_cand; ++slot) UMRS_TEST(slot, cast_covers(r4.x, r4.y, a))
-      n_pairs += n_cand;
     }
 #undef UMRS_TEST
 #undef UMRS_COV_PLAIN
 #undef UMRS_COV_WRAP
-
-    // Careful sweep, only if some ray of the chunk saw two candidates with the
-    // same q: lowest hit index wins (the reference's scan order with a strict <).
+    // spilled candidates (no span check: the coverage predicate is the exact test anyway), or every slot
+    const int n_list = sweep_all ? n_cand : n_wide;
+    const unsigned list_s = sweep_all ? 0u : wide_s;
+    if (n_list > 0) {
+      RayBest b;
+      b.q = best; b.slot = best_s; b.tie = tie;
+      b = slow_candidates(rec_s, list_s, n_list, a, rx, ry, b);
+      best = b.q; best_s = b.slot; tie = b.tie;
+      n_pairs += n_list;
+    }
     if (__any_sync(0xffffffffu, tie != 0)) {
       if (counters != nullptr && lane == 0) atomicAdd(counters + 4, 1ull);
-      int best_idx = best_s >= 0 ? lds_i1_off20(rec_addr((unsigned)best_s, rec_s)) : prev_i;
-      auto careful = [&](int slot) {
-        UMRS_ASSERT(slot >= 0 && slot < n_cand);
-        const unsigned ra = rec_addr((unsigned)slot, rec_s);
-        const float4 r4 = lds_f4(ra);
-        if (!cast_covers(r4.x, r4.y, a)) return;
-        const float q = lds_f1_off16(ra) * rcp_approx(__fmaf_rn(r4.z, rx, r4.w * ry));
-        const int id = lds_i1_off20(ra);
-        if (q == best && id < best_idx) { best_s = slot; best_idx = id; }
-      };
-      if (!sweep_all) {
-        for (int e = 0; e < n_plain; ++e) careful(sm.pool[chunk * K + e]);
-        for (int e = 0; e < n_wrap; ++e) careful(sm.pool[chunk * K + K - 1 - e]);
-        for (int e = 0; e < n_wide; ++e) careful(sm.wide[e]);
-      } else {
-        for (int slot = 0; slot < n_cand; ++slot) careful(slot);
-      }
+      best_s = tie_sweep(rec_s, bucket_s, K, n_plain, n_wrap, list_s, n_list, a, rx, ry, best, best_s, prev_i);
     }
 
     if (live) {
