@@ -409,6 +409,8 @@ int umrs_config_human_params(const umrs_config* cfg, umrs_human_params* out, int
  *                  (cp.async.bulk + mbarrier) instead of per-thread loads; read when a plan is made
  *                  (world creation / scan call).  Only variant builds (-DUMRS_TMA_STAGE) contain the
  *                  code: measured slower on every plan (profiles/r2_tma_ab.txt), no effect otherwise
+ *   "split_step"   -1 auto | 0 | 1: run a world tick as two launches (entity kernel, then the fan
+ *                  kernel on the stepped poses) instead of the fused one; auto splits large batches
  *   "render_cta_fans"  reference render: batches of up to this many fans run one 4-warp CTA per fan
  *                  (the speculative form), larger ones a warp per fan (0 = default)
  * UMRS_ERR_INVALID for an unknown key or a value out of range. */

@@ -605,6 +605,53 @@ def test_cta_shapes_give_the_same_bits(segments):
             assert np.array_equal(a, b), "shape %s differs from the picked shape" % shape
 
 
+def test_two_launch_step_gives_the_fused_step_bits():
+    """A tick can run fused (one kernel: entity steps + scans) or split (k_world_entities, then the
+    fan kernel on the stepped poses; "split_step" tuning, auto for large batches).  Same bits either
+    way: ranges, hit indices, poses, velocities, human poses, object lines and fan parameters, on a
+    crowded roster with every model, humans, a static object, laser + motion noise, over 4 ticks --
+    and on a car-only roster, blocking and pipelined ticks."""
+    segs = umrs.map_cleanup(synth.floorplan_segments(300, extent=60.0, seed=1234))
+    vmap = umrs.VectorMap(lines=segs)
+    rps, hps = _config2_roster()
+    W, R, H = 40, len(rps), len(hps)
+    free = synth.sample_free_poses_fast(segs, W * (R + 2 * H + 1), 60.0, seed=5, clearance=0.5).reshape(W, -1, 3)
+    cmds = np.random.default_rng(3).uniform(-1, 1, (4, W, R, 3)).astype(np.float32)
+    runs = {}
+    for split in (0, 1):
+        with _lib.tuning(split_step=split):
+            wd = umrs.World(vmap, rps, W, humans=hps, static_objects=1, dt=float(DT), seed=77,
+                            laser_noise=True, motion_noise=True)
+            wd.SetPose(free[:, :R])
+            wd.SetHumans(free[:, R:R + H], free[:, R + H:R + 2 * H])
+            wd.SetStaticObjects(free[:, R + 2 * H:])
+            out = []
+            for k in range(4):
+                r, i = wd.Step(cmds[k], want_idx=True)
+                out += [r.view(np.uint32).copy(), i.copy(), wd.GetLines().view(np.uint32).copy(),
+                        wd.fan_params().view(np.uint32).copy()]
+            pose, vel = wd.GetPose()
+            out += [pose.view(np.uint32), vel.view(np.uint32), np.frombuffer(wd.get_state(), np.uint8).copy()]
+        runs[split] = out
+    for a, b in zip(runs[0], runs[1]):
+        assert np.array_equal(a, b)
+    # car-only roster (the instance without the other models), device-resident and pipelined ticks
+    Wc = 700
+    outs = {}
+    for split in (0, 1):
+        with _lib.tuning(split_step=split):
+            world, _, _, _ = _make_car_world(Wc, M=256, noise=True)
+            o = []
+            for step in range(3):
+                r, i = world.Step(synth.ackermann_commands(Wc, 1, step), want_idx=True)
+                o += [r.view(np.uint32).copy(), i.copy()]
+            pose, vel = world.GetPose()
+            o += [pose.view(np.uint32), vel.view(np.uint32)]
+        outs[split] = o
+    for a, b in zip(outs[0], outs[1]):
+        assert np.array_equal(a, b)
+
+
 def test_checkpoint_resume_is_bit_reproducible():
     """umrs_world_get_state / set_state (the reference only has SetPose, simulator.cpp:191-196):
     50 ticks, snapshot, 50 more; restore the snapshot into the same world AND into a fresh one, 50 more

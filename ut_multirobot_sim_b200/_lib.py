@@ -162,7 +162,7 @@ SIGNATURES = {
 
 # Dev convenience for A/B scripts: UMRS_TUNE_<KEY>=<int> in the environment is handed to
 # umrs_tuning_set once, when the library is loaded (the library itself never reads the environment).
-TUNING_KEYS = ("cta_shape", "cap", "grid_from", "step_slices", "tma_stage", "render_cta_fans")
+TUNING_KEYS = ("cta_shape", "cap", "grid_from", "step_slices", "tma_stage", "render_cta_fans", "split_step")
 
 _lib = None
 

@@ -426,6 +426,7 @@ int umrs_tuning_set(const char* key, int32_t value) {
   else if (k == "cap") { if (value != 0 && (value < 32 || value > 4064)) return UMRS_ERR_INVALID; g_tuning.cap = value; }
   else if (k == "grid_from") { if (value < 0) return UMRS_ERR_INVALID; g_tuning.grid_from = value; }
   else if (k == "step_slices") { if (value < 0 || value > 15) return UMRS_ERR_INVALID; g_tuning.step_slices = value; }
+  else if (k == "split_step") { if (value < -1 || value > 1) return UMRS_ERR_INVALID; g_tuning.split_step = value; }
   else if (k == "tma_stage") { if (value < -1 || value > 1) return UMRS_ERR_INVALID; g_tuning.tma_stage = value; }
   else if (k == "render_cta_fans") { if (value < 0) return UMRS_ERR_INVALID; g_tuning.render_cta_fans = value; }
   else return UMRS_ERR_INVALID;
@@ -439,6 +440,7 @@ int umrs_tuning_get(const char* key, int32_t* value) {
   else if (k == "cap") *value = g_tuning.cap;
   else if (k == "grid_from") *value = g_tuning.grid_from;
   else if (k == "step_slices") *value = g_tuning.step_slices;
+  else if (k == "split_step") *value = g_tuning.split_step;
   else if (k == "tma_stage") *value = g_tuning.tma_stage;
   else if (k == "render_cta_fans") *value = g_tuning.render_cta_fans;
   else return UMRS_ERR_INVALID;

@@ -81,6 +81,7 @@ struct Tuning {
   int grid_from = 0;
   int step_slices = 0;
   int tma_stage = -1;   // -1 auto (the plan decides), 0 off, 1 on wherever the plan allows it
+  int split_step = -1;       // world step as entity kernel + scan kernel: -1 auto (large batches), 0 never, 1 always
   int render_cta_fans = 0;   // reference render: batches up to this many fans run one 4-warp CTA per fan (0 = default)
 };
 extern Tuning g_tuning;
@@ -144,6 +145,7 @@ struct WorldStepParams {
   int32_t world_base;
   int32_t laser_noise, motion_noise;
   int32_t skip_scan;         // stop after the entity steps / object lines / fan (reference render follows)
+  int32_t pre_stepped;       // set by the launcher: k_world_entities has run, the fan kernel only scans
   int32_t cars_only;         // every robot is an Ackermann car and there are no humans: the kernel instance
                              // without the other models' code is launched
 };

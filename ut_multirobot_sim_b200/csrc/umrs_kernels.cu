@@ -1206,6 +1206,97 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
   }
 }
 
+// ---- phase A for one entity --------------------------------------------------------
+// Entity e of world w: static objects first, then humans, then robots.  Steps it from the
+// read-only "in" state, stores the "out" state when `write`, returns the post-step pose.
+template <bool kCarsOnly>
+__device__ __forceinline__ void step_entity(const WorldStepParams& p, int w, int e, bool write, double dt,
+                                            float& px, float& py, float& pth) {
+  if (e < p.O) {
+    const float* sp = p.static_pose + ((size_t)w * p.O + e) * 3;
+    px = sp[0]; py = sp[1]; pth = sp[2];
+  } else if (!kCarsOnly && e < p.O + p.H) {
+    const int h = e - p.O;
+    HumanState s = p.hs_in[(size_t)w * p.H + h];
+    human_step(s, p.humans[h], dt);
+    if (write) p.hs_out[(size_t)w * p.H + h] = s;
+    px = s.pose[0]; py = s.pose[1]; pth = s.pose[2];
+  } else {
+    const int rr = e - p.O - p.H;
+    const size_t gi = (size_t)w * p.R + rr;
+    RobotState s = p.rs_in[gi];
+    const umrs_robot_params& rp = p.robots[rr];
+    if (p.cmds != nullptr && (p.cmd_mask == nullptr || p.cmd_mask[gi] != 0)) {
+      const float cmd[3] = {p.cmds[gi * 3 + 0], p.cmds[gi * 3 + 1], p.cmds[gi * 3 + 2]};
+      robot_command<kCarsOnly>(s, rp, cmd);
+    }
+    float n1 = 0.f, n2 = 0.f;
+    if (p.motion_noise && (kCarsOnly || rp.model_type == UMRS_ACKERMANN_DRIVE)) {
+      const uint4 wd = philox4x32(
+          make_uint4(0u, (uint32_t)(p.world_base + w) * (uint32_t)p.R + (uint32_t)rr,
+                     p.step_lo, p.step_hi ^ kStreamMotion),
+          make_uint2(p.key0, p.key1));
+      const float2 g = box_muller(wd.x, wd.y);
+      n1 = g.x; n2 = g.y;
+    }
+    robot_step<kCarsOnly>(s, rp, dt, n1, n2);
+    if (write) {
+      p.rs_out[gi] = s;
+      if (p.robot_pose_out != nullptr) {
+        p.robot_pose_out[gi * 3 + 0] = s.pose[0];
+        p.robot_pose_out[gi * 3 + 1] = s.pose[1];
+        p.robot_pose_out[gi * 3 + 2] = s.pose[2];
+      }
+    }
+    px = s.pose[0]; py = s.pose[1]; pth = s.pose[2];
+  }
+}
+
+// laserLoc = t + Rotation2Df(angle) * (laser_x, laser_y) with sin/cos of the raw pose angle
+// (float overloads inside Eigen), simulator.cpp:398-401
+__device__ __forceinline__ float4 fan_of(const umrs_robot_params& me, float px, float py, float pth,
+                                         float sn, float cs) {
+  return make_float4(px + (cs * me.laser.loc_x - sn * me.laser.loc_y),
+                     py + (sn * me.laser.loc_x + cs * me.laser.loc_y),
+                     me.laser.angle_min + pth, me.laser.angle_max + pth);
+}
+
+// R * template + T (human_object.cpp:135-138)
+__device__ __forceinline__ float4 place_line(const float4 tm, float px, float py, float sn, float cs) {
+  float4 o;
+  o.x = (cs * tm.x - sn * tm.y) + px;
+  o.y = (sn * tm.x + cs * tm.y) + py;
+  o.z = (cs * tm.z - sn * tm.w) + px;
+  o.w = (sn * tm.z + cs * tm.w) + py;
+  return o;
+}
+
+// ---- entity kernel of the two-launch step --------------------------------------------
+// One thread per (world, entity): the step, the entity's object lines and -- for a robot -- its
+// fan, all to global memory; k_world_step<..., kPreStepped> then runs the scans from there.
+// Splitting the tick takes the serial entity step (one thread, ~5 k cycles of double-precision
+// math) off the critical path of every fan CTA; the fused form stays for small batches, where
+// one launch is the shorter path.
+template <bool kCarsOnly>
+__global__ void __launch_bounds__(128)
+k_world_entities(const __grid_constant__ WorldStepParams p) {
+  const int n_ent = p.O + p.H + p.R;
+  const int g = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+  if (g >= p.world_count * n_ent) return;
+  const int w = p.world_first + g / n_ent, e = g % n_ent;
+  float px, py, pth;
+  step_entity<kCarsOnly>(p, w, e, true, (double)p.dt, px, py, pth);
+  const float2 sca = sincos_ref(angle_mod_f(pth));   // HumanObject::Transform rotation, human_object.cpp:132
+  const int l0 = p.ent_off[e], l1 = p.ent_off[e + 1];
+  for (int l = l0; l < l1; ++l)
+    p.obj_lines_out[(size_t)w * p.L_obj + l] = place_line(__ldg(p.tmpl + l), px, py, sca.x, sca.y);
+  if (e >= p.O + p.H) {
+    const int r = e - p.O - p.H;
+    const float2 scl = sincos_ref(pth);
+    p.fan_params[(size_t)w * p.R + r] = fan_of(p.robots[r], px, py, pth, scl.x, scl.y);
+  }
+}
+
 // ---- fused world-step kernel -------------------------------------------------
 // grid = world_count * R fans; CTA (w, r).  Every CTA of world w integrates ALL
 // entities of that world (R + H tiny steps, redundantly across the R CTAs) from
@@ -1213,7 +1304,8 @@ __device__ void human_step(HumanState& s, const umrs_human_params& p, double dt)
 // CTA alone writes the "out" state (ping-pong buffers).  Order as in
 // Simulator::Run (simulator.cpp:531-541): update() first, scan from the
 // post-step pose against the post-step object lines.
-template <int kThreads, int kCtas, bool kCarsOnly, bool kCounters>
+// kPreStepped: k_world_entities has run -- the fan and the object lines come from global memory.
+template <int kThreads, int kCtas, bool kCarsOnly, bool kCounters, bool kPreStepped>
 __global__ void __launch_bounds__(kThreads, kCtas)
 k_world_step(const __grid_constant__ WorldStepParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1225,100 +1317,55 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   const double dt = (double)p.dt;  // `const double& dt` bound to float CONFIG_DT
   const int t = threadIdx.x;
   UMRS_STAMP_INIT;
-  if (kTmaBuilt && p.c.tma_stage != 0 && t == 32 % blockDim.x) {
-    // the map streams into shared memory (copy engine) while thread 0 steps the robot
-    stage_bar_init(sm.ctl + kCtlBar);
-    if (p.c.tma_stage == 1) stage_issue_map(sm, p.c.src);
-  }
-
-  // ---- phase A: entity steps -> sm.ent[e] = {x, y, theta, sin, cos} ----------
-  for (int e = t; e < n_ent; e += blockDim.x) {
-    float px, py, pth;
-    if (e < p.O) {
-      const float* sp = p.static_pose + ((size_t)w * p.O + e) * 3;
-      px = sp[0]; py = sp[1]; pth = sp[2];
-    } else if (!kCarsOnly && e < p.O + p.H) {
-      const int h = e - p.O;
-      HumanState s = p.hs_in[(size_t)w * p.H + h];
-      human_step(s, p.humans[h], dt);
-      if (owner) p.hs_out[(size_t)w * p.H + h] = s;
-      px = s.pose[0]; py = s.pose[1]; pth = s.pose[2];
-    } else {
-      const int rr = e - p.O - p.H;
-      const size_t gi = (size_t)w * p.R + rr;
-      RobotState s = p.rs_in[gi];
-      const umrs_robot_params& rp = p.robots[rr];
-      if (p.cmds != nullptr && (p.cmd_mask == nullptr || p.cmd_mask[gi] != 0)) {
-        const float cmd[3] = {p.cmds[gi * 3 + 0], p.cmds[gi * 3 + 1], p.cmds[gi * 3 + 2]};
-        robot_command<kCarsOnly>(s, rp, cmd);
-      }
-      float n1 = 0.f, n2 = 0.f;
-      if (p.motion_noise && (kCarsOnly || rp.model_type == UMRS_ACKERMANN_DRIVE)) {
-        const uint4 wd = philox4x32(
-            make_uint4(0u, (uint32_t)(p.world_base + w) * (uint32_t)p.R + (uint32_t)rr,
-                       p.step_lo, p.step_hi ^ kStreamMotion),
-            make_uint2(p.key0, p.key1));
-        const float2 g = box_muller(wd.x, wd.y);
-        n1 = g.x; n2 = g.y;
-      }
-      robot_step<kCarsOnly>(s, rp, dt, n1, n2);
-      if (owner) {
-        p.rs_out[gi] = s;
-        if (p.robot_pose_out != nullptr) {
-          p.robot_pose_out[gi * 3 + 0] = s.pose[0];
-          p.robot_pose_out[gi * 3 + 1] = s.pose[1];
-          p.robot_pose_out[gi * 3 + 2] = s.pose[2];
-        }
-      }
-      px = s.pose[0]; py = s.pose[1]; pth = s.pose[2];
-    }
-    // HumanObject::Transform rotation, human_object.cpp:132: R(AngleMod(angle))
-    const float am = angle_mod_f(pth);
-    float* en = sm.ent + 8 * e;
-    en[0] = px; en[1] = py; en[2] = pth;
-    const float2 sca = sincos_ref(am);
-    en[3] = sca.x; en[4] = sca.y;
-    if (e >= p.O + p.H) {   // laser pose of a robot: sin/cos of the raw angle (simulator.cpp:398-401)
-      const float2 scl = sincos_ref(pth);
-      en[5] = scl.x; en[6] = scl.y;
-    }
-  }
-  __syncthreads();
-
-  // ---- object lines: R * template + T (human_object.cpp:135-138) --------------
-  for (int l = t; l < p.L_obj; l += blockDim.x) {
-    const int e = p.line_ent[l];
-    const float4 tm = __ldg(p.tmpl + l);
-    const float* en = sm.ent + 8 * e;
-    const float sn = en[3], cs = en[4];
-    float4 o;
-    o.x = (cs * tm.x - sn * tm.y) + en[0];
-    o.y = (sn * tm.x + cs * tm.y) + en[1];
-    o.z = (cs * tm.z - sn * tm.w) + en[0];
-    o.w = (sn * tm.z + cs * tm.w) + en[1];
-    sm.obj[l] = o;
-    if (owner && p.obj_lines_out != nullptr) p.obj_lines_out[(size_t)w * p.L_obj + l] = o;
-  }
-
-  // ---- fan of robot r (simulator.cpp:398-411) ----------------------------------
   const umrs_robot_params& me = p.robots[r];
-  const float* en = sm.ent + 8 * (p.O + p.H + r);
   Fan fan;
-  {
-    // laserLoc = t + Rotation2Df(angle) * (laser_x, laser_y): sin/cos of the raw
-    // pose angle (float overloads inside Eigen)
-    const float sn = en[5], cs = en[6];
-    fan.lx = en[0] + (cs * me.laser.loc_x - sn * me.laser.loc_y);
-    fan.ly = en[1] + (sn * me.laser.loc_x + cs * me.laser.loc_y);
-    fan.amin = me.laser.angle_min + en[2];
-    fan.amax = me.laser.angle_max + en[2];
-    fan.num_rays = p.num_rays[r];
-    fan.range_max = me.laser.range_max;
+  const float4* obj = sm.obj;
+  if (kPreStepped) {
+    const float4 fp = p.fan_params[(size_t)w * p.R + r];
+    fan.lx = fp.x; fan.ly = fp.y; fan.amin = fp.z; fan.amax = fp.w;
+    obj = p.obj_lines_out + (size_t)w * p.L_obj;
+  } else {
+    if (kTmaBuilt && p.c.tma_stage != 0 && t == 32 % blockDim.x) {
+      // the map streams into shared memory (copy engine) while thread 0 steps the robot
+      stage_bar_init(sm.ctl + kCtlBar);
+      if (p.c.tma_stage == 1) stage_issue_map(sm, p.c.src);
+    }
+
+    // ---- phase A: entity steps -> sm.ent[e] = {x, y, theta, sin, cos} ----------
+    for (int e = t; e < n_ent; e += blockDim.x) {
+      float px, py, pth;
+      step_entity<kCarsOnly>(p, w, e, owner, dt, px, py, pth);
+      // HumanObject::Transform rotation, human_object.cpp:132: R(AngleMod(angle))
+      const float am = angle_mod_f(pth);
+      float* en = sm.ent + 8 * e;
+      en[0] = px; en[1] = py; en[2] = pth;
+      const float2 sca = sincos_ref(am);
+      en[3] = sca.x; en[4] = sca.y;
+      if (e >= p.O + p.H) {   // laser pose of a robot: sin/cos of the raw angle (simulator.cpp:398-401)
+        const float2 scl = sincos_ref(pth);
+        en[5] = scl.x; en[6] = scl.y;
+      }
+    }
+    __syncthreads();
+
+    // ---- object lines: R * template + T (human_object.cpp:135-138) --------------
+    for (int l = t; l < p.L_obj; l += blockDim.x) {
+      const float* en = sm.ent + 8 * p.line_ent[l];
+      const float4 o = place_line(__ldg(p.tmpl + l), en[0], en[1], en[3], en[4]);
+      sm.obj[l] = o;
+      if (owner && p.obj_lines_out != nullptr) p.obj_lines_out[(size_t)w * p.L_obj + l] = o;
+    }
+
+    // ---- fan of robot r (simulator.cpp:398-411) ----------------------------------
+    const float* en = sm.ent + 8 * (p.O + p.H + r);
+    const float4 fp = fan_of(me, en[0], en[1], en[2], en[5], en[6]);
+    fan.lx = fp.x; fan.ly = fp.y; fan.amin = fp.z; fan.amax = fp.w;
+    if (t == 0 && p.fan_params != nullptr) p.fan_params[(size_t)w * p.R + r] = fp;
+    __syncthreads();
+    if (p.skip_scan) return;   // reference-render worlds: the scan is k_scan_reference_render's
   }
-  if (t == 0 && p.fan_params != nullptr)
-    p.fan_params[(size_t)w * p.R + r] = make_float4(fan.lx, fan.ly, fan.amin, fan.amax);
-  __syncthreads();
-  if (p.skip_scan) return;   // reference-render worlds: the scan is k_scan_reference_render's
+  fan.num_rays = p.num_rays[r];
+  fan.range_max = me.laser.range_max;
 
   const int skip_lo = p.ent_off[p.O + p.H + r], skip_hi = p.ent_off[p.O + p.H + r + 1];
   PostProcess post;
@@ -1329,7 +1376,7 @@ k_world_step(const __grid_constant__ WorldStepParams p) {
   post.fan_global = (uint32_t)(p.world_base + w) * (uint32_t)p.R + (uint32_t)r;
   const size_t off = (size_t)w * (size_t)p.rays_per_world + (size_t)p.ray_off[r];
   UMRS_STAMP(p.c.counters, 0);
-  scan_fan(sm, p.c, fan, sm.obj, p.L_obj, skip_lo, skip_hi, p.c.ranges + off,
+  scan_fan(sm, p.c, fan, obj, p.L_obj, skip_lo, skip_hi, p.c.ranges + off,
            p.c.hit_idx ? p.c.hit_idx + off : nullptr, post, 0u, kCounters ? p.c.counters : nullptr);
 }
 
@@ -1407,7 +1454,7 @@ static cudaError_t dev_limits(DevLimits** out) {
 template <int kThreads, int kCtas>
 static bool seats(size_t smem) {
   int n = 0, m = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kThreads, kCtas, false, false>, kThreads, smem) != cudaSuccess ||
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_world_step<kThreads, kCtas, false, false, false>, kThreads, smem) != cudaSuccess ||
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_scan_batch<kThreads, kCtas, false>, kThreads, smem) != cudaSuccess) {
     (void)cudaGetLastError();
     return false;
@@ -1449,10 +1496,13 @@ static cudaError_t configure_shape(DevLimits& d, int shape, size_t smem_bytes) {
   cudaError_t e = cudaFuncSetAttribute(k_scan_batch<kThreads, kCtas, false>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, false, false>,
+  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, false, false, false>,
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, true, false>,
+  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, true, false, false>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k_world_step<kThreads, kCtas, false, false, true>,
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
   d.configured[shape] = smem_bytes;
@@ -1474,8 +1524,9 @@ static cudaError_t launch_step_shape(DevLimits& d, int shape, const WorldStepPar
   cudaError_t e = configure_shape<kThreads, kCtas>(d, shape, smem);
   if (e != cudaSuccess) return e;
   // a roster of Ackermann cars only (and no humans) runs the instance compiled without the other models
-  if (p.cars_only) k_world_step<kThreads, kCtas, true, false><<<fans, kThreads, smem, stream>>>(p);
-  else k_world_step<kThreads, kCtas, false, false><<<fans, kThreads, smem, stream>>>(p);
+  if (p.pre_stepped) k_world_step<kThreads, kCtas, false, false, true><<<fans, kThreads, smem, stream>>>(p);
+  else if (p.cars_only) k_world_step<kThreads, kCtas, true, false, false><<<fans, kThreads, smem, stream>>>(p);
+  else k_world_step<kThreads, kCtas, false, false, false><<<fans, kThreads, smem, stream>>>(p);
   return cudaSuccess;
 }
 
@@ -1522,11 +1573,24 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
   WorldStepParams p = p_in;
   const size_t smem = fill_smem_offsets(p.c, p.L_obj, p.O + p.H + p.R);
   std::lock_guard<std::mutex> lock(g_dev_mutex);   // the per-device shape cache is shared by all handles
-  if (p.c.counters != nullptr) return launch_counted(k_world_step<256, 4, false, true>, 1, p, fans, smem, stream);
+  if (p.c.counters != nullptr) return launch_counted(k_world_step<256, 4, false, true, false>, 1, p, fans, smem, stream);
   DevLimits* d = nullptr;
   cudaError_t e = dev_limits(&d);
   if (e != cudaSuccess) return e;
   const int shape = pick_shape(*d, smem, fans);
+  // Two-launch step (umrs_tuning "split_step": -1 auto, 0 never, 1 always): worth a second launch
+  // once the fans fill the SMs several times over; reference-render worlds are split already.
+  const bool can_split = !p.skip_scan && p.fan_params != nullptr && p.obj_lines_out != nullptr;
+  const bool split = can_split && (g_tuning.split_step > 0 ||
+                                   (g_tuning.split_step < 0 && (long long)fans >= 4LL * shape_ctas(shape) * d->n_sm));
+  if (split) {
+    const int n_thr = p.world_count * (p.O + p.H + p.R);
+    if (p.cars_only) k_world_entities<true><<<(n_thr + 127) / 128, 128, 0, stream>>>(p);
+    else k_world_entities<false><<<(n_thr + 127) / 128, 128, 0, stream>>>(p);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    note_launch();
+    p.pre_stepped = 1;
+  }
   switch (shape) {
     case kShape96x10: e = launch_step_shape<96, 10>(*d, shape, p, fans, smem, stream); break;
     case kShape128x8: e = launch_step_shape<128, 8>(*d, shape, p, fans, smem, stream); break;
