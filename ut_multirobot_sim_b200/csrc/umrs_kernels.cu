@@ -1579,10 +1579,11 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
   if (e != cudaSuccess) return e;
   const int shape = pick_shape(*d, smem, fans);
   // Two-launch step (umrs_tuning "split_step": -1 auto, 0 never, 1 always): worth a second launch
-  // once the fans fill the SMs several times over; reference-render worlds are split already.
+  // once the fans fill the SMs more than twice over (measured break-even: two resident waves, at
+  // 256 x 4 as at 96 x 10); reference-render worlds are split already.
   const bool can_split = !p.skip_scan && p.fan_params != nullptr && p.obj_lines_out != nullptr;
   const bool split = can_split && (g_tuning.split_step > 0 ||
-                                   (g_tuning.split_step < 0 && (long long)fans >= 4LL * shape_ctas(shape) * d->n_sm));
+                                   (g_tuning.split_step < 0 && (long long)fans > 2LL * shape_ctas(shape) * d->n_sm));
   if (split) {
     const int n_thr = p.world_count * (p.O + p.H + p.R);
     if (p.cars_only) k_world_entities<true><<<(n_thr + 127) / 128, 128, 0, stream>>>(p);
