@@ -41,6 +41,10 @@
 #include "umrs_device.cuh"
 #include "umrs_internal.h"
 
+#ifndef UMRS_GATHER_DEPTH
+#define UMRS_GATHER_DEPTH 2
+#endif
+
 
 // Dev build (-DUMRS_PHASE_TIMING): thread 0 of every fan CTA adds the clock64 cycles between
 // phase boundaries to counters[8 + k] (k: 0 world phase A, 1 setup, 2 gather, 3 records,
@@ -333,6 +337,7 @@ __device__ __noinline__ float2 sincos_ref(float a) { return make_float2(sinf(a),
 
 constexpr float kWedgeMargin = 1e-3f;   // rad; dominates every rounding in the wedge test by 1000x
 
+constexpr int kGatherDepth = UMRS_GATHER_DEPTH;
 // ---- S1: gather + AABB cull + compaction ------------------------------------------
 // Virtual indices [v_begin, v_end) of this pass.  Object lines [skip_lo, skip_hi)
 // are the fan's own body.
@@ -348,48 +353,61 @@ __device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
   const bool wedge_on = sm.ctl[kCtlWedgeOn] != 0;
   const float* wf = reinterpret_cast<const float*>(sm.ctl + kCtlWedge);
   const float e1x = wf[0], e1y = wf[1], e2x = wf[2], e2y = wf[3];
-  // iterate in warp-uniform trip counts so that the ballots are full-warp
-  for (int vb = v_begin + (int)(threadIdx.x & ~31u); vb < v_end; vb += blockDim.x) {
-    const int v = vb + lane;
-    bool keep = false;
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    int hit = -1;
-    if (v < v_end) {
-      // row of v: the table is short (2 rows for K1, a few dozen for K2)
-      int lo = 0, hi = n_rows - 1;
-      while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (sm.row_v0[mid] <= v) lo = mid; else hi = mid - 1;
+  // Warp-uniform trip counts (the ballots are full-warp), kGatherDepth trips at a time: their
+  // loads are issued back to back, so a fan pays one L2 round trip per kGatherDepth trips (the
+  // fan's critical path is what the launch's time follows -- DESIGN 4.2).
+  const int nt = (int)blockDim.x;
+  for (int vb0 = v_begin + (int)(threadIdx.x & ~31u); vb0 < v_end; vb0 += kGatherDepth * nt) {
+    float4 s[kGatherDepth];
+    int hit[kGatherDepth];
+    bool keep[kGatherDepth];
+#pragma unroll
+    for (int u = 0; u < kGatherDepth; ++u) {
+      const int v = vb0 + u * nt + lane;
+      keep[u] = false;
+      s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      hit[u] = -1;
+      if (v < v_end) {
+        // row of v: the table is short (2 rows for K1, a few dozen for K2)
+        int lo = 0, hi = n_rows - 1;
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (sm.row_v0[mid] <= v) lo = mid; else hi = mid - 1;
+        }
+        const int k = v - sm.row_v0[lo];
+        if (lo == n_rows - 1) {
+          s[u] = obj_segs[k];
+          hit[u] = src.n_map_total + k;
+          keep[u] = !(k >= skip_lo && k < skip_hi);
+        } else {
+          const int si = sm.row_s0[lo] + k;
+          s[u] = staged ? sm.stage[v] : __ldg(src.segs + si);   // K1: v == si; K2: rows are staged back to back
+          hit[u] = src.orig ? __ldg(src.orig + si) : si;
+          keep[u] = true;
+        }
       }
-      const int k = v - sm.row_v0[lo];
-      if (lo == n_rows - 1) {
-        s = obj_segs[k];
-        hit = src.n_map_total + k;
-        keep = !(k >= skip_lo && k < skip_hi);
-      } else {
-        const int si = sm.row_s0[lo] + k;
-        s = staged ? sm.stage[v] : __ldg(src.segs + si);   // K1: v == si; K2: rows are staged back to back
-        hit = src.orig ? __ldg(src.orig + si) : si;
-        keep = true;
-      }
-      keep = keep && aabb_keep(s, fan.lx, fan.ly, fan.range_max);
+    }
+#pragma unroll
+    for (int u = 0; u < kGatherDepth; ++u) {
+      if (vb0 + u * nt >= v_end) break;   // warp-uniform
+      bool kp = keep[u] && aabb_keep(s[u], fan.lx, fan.ly, fan.range_max);
+      const float ax = s[u].x - fan.lx, ay = s[u].y - fan.ly, bx = s[u].z - fan.lx, by = s[u].w - fan.ly;
       if (wedge_on) {
-        const float ax = s.x - fan.lx, ay = s.y - fan.ly, bx = s.z - fan.lx, by = s.w - fan.ly;
         // cross(e1, p) > 0 && cross(p, e2) > 0 for p = a, b (NaN compares false: kept)
         const bool in_a = __fmaf_rn(e1x, ay, -(e1y * ax)) > 0.f && __fmaf_rn(ax, e2y, -(ay * e2x)) > 0.f;
         const bool in_b = __fmaf_rn(e1x, by, -(e1y * bx)) > 0.f && __fmaf_rn(bx, e2y, -(by * e2x)) > 0.f;
-        keep = keep && !(in_a && in_b);
+        kp = kp && !(in_a && in_b);
       }
-    }
-    const unsigned m = __ballot_sync(0xffffffffu, keep);
-    int base = 0;
-    if (lane == 0 && m) base = atomicAdd(&sm.ctl[kCtlNCand], __popc(m));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (keep) {
-      const int pos = base + __popc(m & ((1u << lane) - 1u));
-      // translate by -loc (vector_map.cpp:447-448)
-      sm.rec[2 * pos] = make_float4(s.x - fan.lx, s.y - fan.ly, s.z - fan.lx, s.w - fan.ly);
-      sm.rec[2 * pos + 1] = make_float4(0.f, __int_as_float(hit), 0.f, 0.f);
+      const unsigned m = __ballot_sync(0xffffffffu, kp);
+      int base = 0;
+      if (lane == 0 && m) base = atomicAdd(&sm.ctl[kCtlNCand], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (kp) {
+        const int pos = base + __popc(m & ((1u << lane) - 1u));
+        // translate by -loc (vector_map.cpp:447-448)
+        sm.rec[2 * pos] = make_float4(ax, ay, bx, by);
+        sm.rec[2 * pos + 1] = make_float4(0.f, __int_as_float(hit[u]), 0.f, 0.f);
+      }
     }
   }
 }
