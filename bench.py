@@ -74,7 +74,7 @@ def total_worlds(args):
 def workload_name(args):
     w = total_worlds(args)
     return ("config5 shard (65,536 worlds over 8 GPUs = %d per GPU; config3 is --worlds 4096): %d worlds x 1 "
-            "Ackermann x %d rays on %d GPU(s), fused step+scan, floor plan %d segs" % (
+            "Ackermann x %d rays on %d GPU(s), entity step + scan per tick, floor plan %d segs" % (
                 WORLDS_PER_GPU, w, N_RAYS, max(1, args.gpus), args.map_segments))
 
 

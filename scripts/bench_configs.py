@@ -117,7 +117,7 @@ def config2(worlds=(1, 1024), iters=50, cpu=True):
         cnt = world.read_counters()
         world.enable_counters(False)
         o = {"config": 2, "what": "8 robots (3 jackal 3601 rays, 3 bwibot, 2 cobot) + 16 humans + 1 object per world, "
-                                  "1500-seg campus map, fused step, noise on",
+                                  "1500-seg campus map, step + scan (fused for 1 world, two launches for 1024), noise on",
              "worlds": W, "rays_per_world": world.rays_per_world, "ms_per_step": ms, "rays_per_s": rays / ms * 1e3,
              "env_steps_per_s": W / ms * 1e3, "tests_per_ray": cnt["ray_seg_tests"] / rays,
              "segs_prepared_per_fan": cnt["segs_prepared"] / (W * 8)}
