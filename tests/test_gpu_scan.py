@@ -233,6 +233,9 @@ def test_multipass_when_candidates_exceed_the_slots(oracle, kernel):
     assert lib.umrs_tuning_set(b"cap", 7) == _lib.ERR_INVALID
     assert lib.umrs_tuning_set(b"cta_shape", 9) == _lib.ERR_INVALID
     assert lib.umrs_tuning_set(b"no_such_key", 1) == _lib.ERR_INVALID
+    assert lib.umrs_tuning_set(b"split_step", 2) == _lib.ERR_INVALID
+    v = C.c_int32(7)
+    assert lib.umrs_tuning_get(b"split_step", C.byref(v)) == 0 and v.value == -1
 
 
 def test_grid_kernel_with_long_segments_and_far_poses(oracle):

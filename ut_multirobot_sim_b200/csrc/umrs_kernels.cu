@@ -387,27 +387,35 @@ __device__ void gather(const SmemView& sm, const MapSource& src, const Fan& fan,
         }
       }
     }
+    // cull every trip of the group, then ONE slot reservation (a returning shared atomic) for all of them
+    unsigned m[kGatherDepth];
+    int total = 0;
 #pragma unroll
     for (int u = 0; u < kGatherDepth; ++u) {
-      if (vb0 + u * nt >= v_end) break;   // warp-uniform
       bool kp = keep[u] && aabb_keep(s[u], fan.lx, fan.ly, fan.range_max);
-      const float ax = s[u].x - fan.lx, ay = s[u].y - fan.ly, bx = s[u].z - fan.lx, by = s[u].w - fan.ly;
+      // translate by -loc (vector_map.cpp:447-448)
+      s[u] = make_float4(s[u].x - fan.lx, s[u].y - fan.ly, s[u].z - fan.lx, s[u].w - fan.ly);
       if (wedge_on) {
         // cross(e1, p) > 0 && cross(p, e2) > 0 for p = a, b (NaN compares false: kept)
-        const bool in_a = __fmaf_rn(e1x, ay, -(e1y * ax)) > 0.f && __fmaf_rn(ax, e2y, -(ay * e2x)) > 0.f;
-        const bool in_b = __fmaf_rn(e1x, by, -(e1y * bx)) > 0.f && __fmaf_rn(bx, e2y, -(by * e2x)) > 0.f;
+        const bool in_a = __fmaf_rn(e1x, s[u].y, -(e1y * s[u].x)) > 0.f && __fmaf_rn(s[u].x, e2y, -(s[u].y * e2x)) > 0.f;
+        const bool in_b = __fmaf_rn(e1x, s[u].w, -(e1y * s[u].z)) > 0.f && __fmaf_rn(s[u].z, e2y, -(s[u].w * e2x)) > 0.f;
         kp = kp && !(in_a && in_b);
       }
-      const unsigned m = __ballot_sync(0xffffffffu, kp);
-      int base = 0;
-      if (lane == 0 && m) base = atomicAdd(&sm.ctl[kCtlNCand], __popc(m));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (kp) {
-        const int pos = base + __popc(m & ((1u << lane) - 1u));
-        // translate by -loc (vector_map.cpp:447-448)
-        sm.rec[2 * pos] = make_float4(ax, ay, bx, by);
+      keep[u] = kp;
+      m[u] = __ballot_sync(0xffffffffu, kp);   // (lanes beyond v_end hold keep = false)
+      total += __popc(m[u]);
+    }
+    int base = 0;
+    if (lane == 0 && total) base = atomicAdd(&sm.ctl[kCtlNCand], total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+    for (int u = 0; u < kGatherDepth; ++u) {
+      if (keep[u]) {
+        const int pos = base + __popc(m[u] & ((1u << lane) - 1u));
+        sm.rec[2 * pos] = s[u];
         sm.rec[2 * pos + 1] = make_float4(0.f, __int_as_float(hit[u]), 0.f, 0.f);
       }
+      base += __popc(m[u]);
     }
   }
 }
