@@ -1,6 +1,6 @@
 // Scan kernels (K1 shared-memory scan, K2 uniform-grid walk) and the fused world
 // step, sm_100a.  One CTA = one ray fan (one robot's LaserScan of one world), in one of
-// four CTA shapes (threads x resident CTAs per SM) picked per launch: see the launchers.
+// five CTA shapes (threads x resident CTAs per SM) picked per launch: see the launchers.
 //
 // Replaces
 //   VectorMap::GetPredictedScan   vector_map.cpp:420-478   (per-ray fill)
@@ -13,7 +13,9 @@
 //
 // Phases of a CTA (scan_fan):
 //   A  (world step only) integrate every entity of the world, build the
-//      world's object lines in shared memory
+//      world's object lines in shared memory -- or, for large batches, read the
+//      fan and the object lines k_world_entities left in global memory (the
+//      two-launch tick: the serial entity step leaves every fan's critical path)
 //   then, per PASS over at most `cap` source segments (one pass unless the
 //   fan's source set is larger than the shared-memory slots):
 //   S1 gather: threads stream the fan's source rows (the whole map for K1; the
