@@ -783,11 +783,11 @@ __device__ void ray_loop(const SmemView& sm, const Fan& fan, const Lattice& L, i
   const unsigned pool_s = (unsigned)__cvta_generic_to_shared(sm.pool);
   const unsigned wide_s = (unsigned)__cvta_generic_to_shared(sm.wide);
 
-  // Chunks are dealt round-robin to the warps.  (A shared ticket -- atomicAdd + shuffle per chunk --
-  // balanced no better on K1 plans, whose chunk costs are dominated by the fixed part, the ray
-  // directions, and cost the 64 / 256-segment maps 5 / 3 %; the grid walk liked it 2 % better.)
-  const int n_warps = (int)(blockDim.x >> 5);
-  for (int chunk = (int)(threadIdx.x >> 5); chunk < n_chunks; chunk += n_warps) {
+  for (;;) {
+    int chunk = 0;
+    if (lane == 0) chunk = atomicAdd(&sm.ctl[kCtlNextChunk], 1);
+    chunk = __shfl_sync(0xffffffffu, chunk, 0);
+    if (chunk >= n_chunks) break;
     const int i = (chunk << 5) + lane;
     const bool live = i < fan.num_rays;
     float a = __int_as_float(0x7fc00000);  // NaN: covers nothing
