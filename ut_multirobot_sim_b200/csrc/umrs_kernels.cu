@@ -1457,7 +1457,7 @@ __global__ void k3_stats(const float* __restrict__ ranges, size_t n, double* out
 // that count keeps the widest CTA (a single scan runs fastest on 256 threads).  The
 // 1024-segment bench map (52.4 KB) stays at 256 x 4: squeezed to 44 KB (per-ray winners
 // kept in dead record fields) and run as 192 x 5 it was 2.5 % slower, so that was dropped.
-enum { kShape256x4 = 0, kShape192x5 = 1, kShape192x6 = 2, kShape128x8 = 3, kShape96x10 = 4, kNumShapes = 5 };
+enum { kShape256x4 = 0, kShape192x5 = 1, kShape192x6 = 2, kShape128x8 = 3, kShape96x10 = 4, kShape512x2 = 5, kNumShapes = 6 };
 struct DevLimits {
   int n_sm; bool known;
   size_t configured[kNumShapes];
@@ -1490,8 +1490,11 @@ static bool seats(size_t smem) {
   return n >= kCtas && m >= kCtas;
 }
 
+constexpr size_t kWideCtaFrom = 76 * 1024;   // above this only two CTAs fit the 227 KB of an SM
+
 static int shape_ctas(int shape) {
-  return shape == kShape96x10 ? 10 : shape == kShape128x8 ? 8 : shape == kShape192x6 ? 6 : shape == kShape192x5 ? 5 : 4;
+  return shape == kShape96x10 ? 10 : shape == kShape128x8 ? 8 : shape == kShape192x6 ? 6 : shape == kShape192x5 ? 5 :
+         shape == kShape512x2 ? 2 : 4;
 }
 
 static int pick_shape(DevLimits& d, size_t smem, int fans) {
@@ -1508,13 +1511,17 @@ static int pick_shape(DevLimits& d, size_t smem, int fans) {
       else if (seats<192, 6>(smem)) c = kShape192x6;
       // 192 x 5 (37-44.6 KB) is not picked: the gain of a smaller CTA shrinks as the
       // candidate count grows, and at 1024 segments 192 x 5 lost 2.5 % to 256 x 4
+    } else if (smem > kWideCtaFrom) {
+      // plans so large that only two fans fit an SM (3601-ray fans on a 1500-segment map: 115 KB): 256
+      // threads a fan would leave the SM at 16 warps -- twice the threads per fan instead
+      c = kShape512x2;
     }
     d.pick_smem = smem;
     d.pick = c;
     d.pick_known = true;
   }
   // the grid must fill every SM at (almost) the shape's CTA count for the smaller CTA to pay
-  if ((long long)fans < (long long)(shape_ctas(d.pick) - 1) * d.n_sm) return kShape256x4;
+  if (d.pick != kShape512x2 && (long long)fans < (long long)(shape_ctas(d.pick) - 1) * d.n_sm) return kShape256x4;
   return d.pick;
 }
 
@@ -1588,6 +1595,7 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) 
     case kShape128x8: e = launch_scan_shape<128, 8>(*d, shape, p, smem, stream); break;
     case kShape192x6: e = launch_scan_shape<192, 6>(*d, shape, p, smem, stream); break;
     case kShape192x5: e = launch_scan_shape<192, 5>(*d, shape, p, smem, stream); break;
+    case kShape512x2: e = launch_scan_shape<512, 2>(*d, shape, p, smem, stream); break;
     default: e = launch_scan_shape<256, 4>(*d, shape, p, smem, stream); break;
   }
   if (e != cudaSuccess) return e;
@@ -1625,6 +1633,7 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
     case kShape128x8: e = launch_step_shape<128, 8>(*d, shape, p, fans, smem, stream); break;
     case kShape192x6: e = launch_step_shape<192, 6>(*d, shape, p, fans, smem, stream); break;
     case kShape192x5: e = launch_step_shape<192, 5>(*d, shape, p, fans, smem, stream); break;
+    case kShape512x2: e = launch_step_shape<512, 2>(*d, shape, p, fans, smem, stream); break;
     default: e = launch_step_shape<256, 4>(*d, shape, p, fans, smem, stream); break;
   }
   if (e != cudaSuccess) return e;
