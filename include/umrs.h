@@ -400,7 +400,7 @@ int umrs_config_human_params(const umrs_config* cfg, umrs_human_params* out, int
 
 /* ---- tuning hooks (experiments and tests; process-wide; the library never reads the
  * environment) -------------------------------------------------------------------------
- *   "cta_shape"    -1 auto | 0..5: force one fan-CTA shape (256x4, 192x5, 192x6, 128x8, 96x10, 512x2);
+ *   "cta_shape"    -1 auto | 0..6: force one fan-CTA shape (256x4, 192x5, 192x6, 128x8, 96x10, 512x2, 320x3);
  *                  a shape the plan's shared memory cannot seat is ignored
  *   "cap"          candidate slots per pass, 32..4064 (0 = default 1536)
  *   "grid_from"    map size from which the uniform-grid walk is picked (0 = default 4096)

@@ -581,15 +581,15 @@ def test_pipelined_async_ticks_equal_synchronous_ticks():
 
 @pytest.mark.parametrize("segments", [64, 1024])
 def test_cta_shapes_give_the_same_bits(segments):
-    """The fan kernels exist in six CTA shapes (256x4, 192x5, 192x6, 128x8, 96x10, 512x2 threads x
+    """The fan kernels exist in seven CTA shapes (256x4, 192x5, 192x6, 128x8, 96x10, 512x2, 320x3 threads x
     CTAs per SM) and a launch picks one from its shared-memory plan and
     grid size.  The "cta_shape" tuning hook forces one: ranges, hit indices and poses of three
-    noisy ticks, and a scan batch over the same map, must be bit-identical in all six and
+    noisy ticks, and a scan batch over the same map, must be bit-identical in all seven and
     in the picked one (a 1024-world grid on the 64-segment map picks 96x10, the
     1024-segment map 256x4)."""
     W = 1200
     runs = {}
-    for shape in (-1, 0, 1, 2, 3, 4, 5):
+    for shape in (-1, 0, 1, 2, 3, 4, 5, 6):
         with _lib.tuning(cta_shape=shape):
             world, segs, car, vmap = _make_car_world(W, M=segments, noise=True)
             out = []
@@ -600,7 +600,7 @@ def test_cta_shapes_give_the_same_bits(segments):
             fans = world.fan_params().reshape(-1, 4)[:160]
             rb, ib = vmap.ScanBatch(fans, 100.0, 1081, return_index=True)
         runs[shape] = out + [pose.view(np.uint32), vel.view(np.uint32), rb.view(np.uint32), ib]
-    for shape in (0, 1, 2, 3, 4, 5):
+    for shape in (0, 1, 2, 3, 4, 5, 6):
         for a, b in zip(runs[-1], runs[shape]):
             assert np.array_equal(a, b), "shape %s differs from the picked shape" % shape
 

@@ -422,7 +422,7 @@ int umrs_map_check(umrs_map* m) {
 int umrs_tuning_set(const char* key, int32_t value) {
   if (key == NULL) return UMRS_ERR_INVALID;
   const std::string k(key);
-  if (k == "cta_shape") { if (value < -1 || value > 5) return UMRS_ERR_INVALID; g_tuning.cta_shape = value; }
+  if (k == "cta_shape") { if (value < -1 || value > 6) return UMRS_ERR_INVALID; g_tuning.cta_shape = value; }
   else if (k == "cap") { if (value != 0 && (value < 32 || value > 4064)) return UMRS_ERR_INVALID; g_tuning.cap = value; }
   else if (k == "grid_from") { if (value < 0) return UMRS_ERR_INVALID; g_tuning.grid_from = value; }
   else if (k == "step_slices") { if (value < 0 || value > 15) return UMRS_ERR_INVALID; g_tuning.step_slices = value; }

@@ -1457,9 +1457,9 @@ __global__ void k3_stats(const float* __restrict__ ranges, size_t n, double* out
 // that count keeps the widest CTA (a single scan runs fastest on 256 threads).  The
 // 1024-segment bench map (52.4 KB) stays at 256 x 4: squeezed to 44 KB (per-ray winners
 // kept in dead record fields) and run as 192 x 5 it was 2.5 % slower, so that was dropped.
-enum { kShape256x4 = 0, kShape192x5 = 1, kShape192x6 = 2, kShape128x8 = 3, kShape96x10 = 4, kShape512x2 = 5, kNumShapes = 6 };
+enum { kShape256x4 = 0, kShape192x5 = 1, kShape192x6 = 2, kShape128x8 = 3, kShape96x10 = 4, kShape512x2 = 5, kShape320x3 = 6, kNumShapes = 7 };
 struct DevLimits {
-  int n_sm; bool known;
+  int n_sm; int smem_per_sm; bool known;
   size_t configured[kNumShapes];
   size_t pick_smem; int pick; bool pick_known;
 };
@@ -1473,6 +1473,7 @@ static cudaError_t dev_limits(DevLimits** out) {
   DevLimits& d = g_dev[dev & 63];
   if (!d.known) {
     if ((e = cudaDeviceGetAttribute(&d.n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&d.smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev)) != cudaSuccess) return e;
     d.known = true;
   }
   *out = &d;
@@ -1494,7 +1495,7 @@ constexpr size_t kWideCtaFrom = 76 * 1024;   // above this only two CTAs fit the
 
 static int shape_ctas(int shape) {
   return shape == kShape96x10 ? 10 : shape == kShape128x8 ? 8 : shape == kShape192x6 ? 6 : shape == kShape192x5 ? 5 :
-         shape == kShape512x2 ? 2 : 4;
+         shape == kShape512x2 ? 2 : shape == kShape320x3 ? 3 : 4;
 }
 
 static int pick_shape(DevLimits& d, size_t smem, int fans) {
@@ -1515,6 +1516,10 @@ static int pick_shape(DevLimits& d, size_t smem, int fans) {
       // plans so large that only two fans fit an SM (3601-ray fans on a 1500-segment map: 115 KB): 256
       // threads a fan would leave the SM at 16 warps -- twice the threads per fan instead
       c = kShape512x2;
+    } else if (4 * (smem + 1024) > (size_t)d.smem_per_sm) {   // four CTAs (+1 KB each, reserved) do not fit
+      // three fans per SM (1100-1536-segment maps, the 100k-segment grid walk): 320 threads a fan put
+      // 30 warps on the SM instead of 24 (+4-8 %; 512 x 2 loses 6-11 % here)
+      c = kShape320x3;
     }
     d.pick_smem = smem;
     d.pick = c;
@@ -1596,6 +1601,7 @@ cudaError_t launch_scan_batch(const ScanBatchParams& p_in, cudaStream_t stream) 
     case kShape192x6: e = launch_scan_shape<192, 6>(*d, shape, p, smem, stream); break;
     case kShape192x5: e = launch_scan_shape<192, 5>(*d, shape, p, smem, stream); break;
     case kShape512x2: e = launch_scan_shape<512, 2>(*d, shape, p, smem, stream); break;
+    case kShape320x3: e = launch_scan_shape<320, 3>(*d, shape, p, smem, stream); break;
     default: e = launch_scan_shape<256, 4>(*d, shape, p, smem, stream); break;
   }
   if (e != cudaSuccess) return e;
@@ -1634,6 +1640,7 @@ cudaError_t launch_world_step(const WorldStepParams& p_in, cudaStream_t stream) 
     case kShape192x6: e = launch_step_shape<192, 6>(*d, shape, p, fans, smem, stream); break;
     case kShape192x5: e = launch_step_shape<192, 5>(*d, shape, p, fans, smem, stream); break;
     case kShape512x2: e = launch_step_shape<512, 2>(*d, shape, p, fans, smem, stream); break;
+    case kShape320x3: e = launch_step_shape<320, 3>(*d, shape, p, fans, smem, stream); break;
     default: e = launch_step_shape<256, 4>(*d, shape, p, fans, smem, stream); break;
   }
   if (e != cudaSuccess) return e;
