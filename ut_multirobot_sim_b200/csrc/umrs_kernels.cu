@@ -1,6 +1,6 @@
 // Scan kernels (K1 shared-memory scan, K2 uniform-grid walk) and the fused world
 // step, sm_100a.  One CTA = one ray fan (one robot's LaserScan of one world), in one of
-// five CTA shapes (threads x resident CTAs per SM) picked per launch: see the launchers.
+// seven CTA shapes (threads x resident CTAs per SM) picked per launch: see the launchers.
 //
 // Replaces
 //   VectorMap::GetPredictedScan   vector_map.cpp:420-478   (per-ray fill)
