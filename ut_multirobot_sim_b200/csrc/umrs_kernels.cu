@@ -1525,6 +1525,9 @@ static int pick_shape(DevLimits& d, size_t smem, int fans) {
     d.pick = c;
     d.pick_known = true;
   }
+  // a grid that is resident all at once even at two CTAs per SM is a latency question: the widest CTA
+  // (one 1081-ray scan 47 -> 38 us through the host-buffer call, a 148-world tick 29 -> 24 us)
+  if ((long long)fans <= 2LL * d.n_sm) return kShape512x2;
   // the grid must fill every SM at (almost) the shape's CTA count for the smaller CTA to pay
   if (d.pick != kShape512x2 && (long long)fans < (long long)(shape_ctas(d.pick) - 1) * d.n_sm) return kShape256x4;
   return d.pick;
